@@ -1,0 +1,281 @@
+/* include/sblas_b200.h — the C ABI of libsblas_b200.so (B200 / sm_100a).
+ *
+ * This is the drop-in boundary for the multi-GPU CSR SpMV / SpMM hot path of
+ * tartarughina/S-BLAS.  The reference has no FFI layer of its own (header-only C++
+ * templates); the entry points below are what a binding for that path
+ * would bind, and each one cites the reference interface (file:line in the reference
+ * checkout) it replaces.  The C++ drop-in headers next to this file (sblas.h, spmv.h,
+ * spmm.h, matrix.h, matrix_um.h, kernel.h, utility.h, config.h) are thin inline
+ * wrappers over exactly these symbols.
+ *
+ * Conventions
+ *  - plain pointers and sizes only; `stream` is a cudaStream_t passed as void*
+ *    (NULL = the legacy default stream); device pointers belong to the CUDA device that
+ *    is current on the calling thread unless the function takes per-GPU pointer arrays;
+ *  - every function returns 0 on success, non-zero on failure; sblas_last_error()
+ *    returns the message of the last failure on the calling thread;
+ *  - there is NO CPU fallback: without a CUDA device every compute entry point fails;
+ *  - IdxType is int32 (the only index type the reference's tests instantiate,
+ *    unit_test.cu:81, spmv_test.cu:28), DataType is f32 or f64 (utility.h:304-306).
+ */
+#ifndef SBLAS_B200_H
+#define SBLAS_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define SBLAS_API __attribute__((visibility("default")))
+#else
+#define SBLAS_API
+#endif
+
+#define SBLAS_MAX_GPU 16
+
+/* ---- status ------------------------------------------------------------------ */
+SBLAS_API int sblas_version(void);
+SBLAS_API const char* sblas_last_error(void);
+/* number of visible CUDA devices (0 when there is no driver/GPU) */
+SBLAS_API int sblas_device_count(void);
+
+/* ---- launch options ------------------------------------------------------------ */
+enum {
+  SBLAS_VARIANT_AUTO = 0,
+  SBLAS_SPMV_TILE = 1,    /* nnz-balanced row-aligned merge-path tiles, smem-staged products */
+  SBLAS_SPMV_VECTOR = 2,  /* sub-warp (2..32 lanes) per row, no plan needed */
+  SBLAS_SPMV_SPLIT = 3,   /* merge-path tiles that split long rows, carry fix-up (skewed inputs) */
+  SBLAS_SPMM_ROWMAJOR = 1, /* internal row-major B/C: one lane group per A row, 128-bit B gathers */
+  SBLAS_SPMM_COLMAJOR = 2  /* native col-major B/C (the reference's host layout), no transposes */
+};
+enum {
+  SBLAS_FLAG_FMA = 1,          /* allow fused multiply-add (default: separately rounded mul/add
+                                  in the sequential paths, bit-identical to spmv.h:22-31 /
+                                  spmm.h:56-68 on the CPU) */
+  SBLAS_FLAG_HEAD_PARTIAL = 2, /* local row 0 continues a row begun on the previous GPU
+                                  (matrix.h:443-445): its sum goes to carry[0..k), not to y/C */
+  SBLAS_FLAG_TAIL_PARTIAL = 4, /* local last row continues on the next GPU: sum -> carry[k..2k) */
+  SBLAS_FLAG_NO_L1 = 8         /* gather x/B with L1::no_allocate */
+};
+enum { SBLAS_ROW_MAJOR = 0, SBLAS_COL_MAJOR = 1 }; /* = MajorOrder, matrix.h:37 */
+
+typedef struct sblasOpts {
+  int32_t variant;   /* SBLAS_VARIANT_AUTO or one of the enums above */
+  int32_t flags;     /* SBLAS_FLAG_* */
+  int32_t tile;      /* tile size in merge items, 0 = auto */
+  int32_t lanes;     /* lanes per row for the vector variants, 0 = auto */
+  int32_t n_replica; /* extra copies of the output to store (peer GPUs' replicas), <= 15 */
+  int32_t reserved;
+  void* replica[SBLAS_MAX_GPU - 1]; /* same logical base pointer as y / C on each peer */
+  void* carry;       /* device buffer of 2*k DataType for HEAD/TAIL partial sums */
+} sblasOpts;
+
+/* ---- integer layer: partitioners (host, bit-exact with the reference) ------------- */
+/* utility.h:293-300 csr_findRowIdxUsingNnzIdx — row i with rowptr[i] <= idx < rowptr[i+1]
+ * (empty rows skipped), -1 if none.  Binary search instead of the reference's O(h) scan. */
+SBLAS_API int32_t sblas_csr_find_row_i32(const int32_t* rowptr, int32_t height, int32_t nnz_idx);
+
+/* matrix.h:360-369 CsrSparseMatrix::sync2gpu(segment): nnz split.  avg_nnz uses integer
+ * ceil-div (the reference's float32 ceil agrees whenever it is exact).
+ * Outputs have n_gpu entries. */
+SBLAS_API int sblas_csr_partition_nnz_i32(const int32_t* rowptr, int32_t height, int32_t nnz,
+                                          unsigned n_gpu, int32_t* avg_nnz, int32_t* nnz_gpu,
+                                          int32_t* starting_row_gpu, int32_t* stoping_row_gpu);
+/* matrix.h:370-375: GPU i's local row-pointer array (stop-start+2 entries, :398-404). */
+SBLAS_API int sblas_csr_segment_rowptr_i32(const int32_t* rowptr, int32_t avg_nnz, unsigned i_gpu,
+                                           int32_t starting_row, int32_t stoping_row,
+                                           int32_t nnz_gpu_i, int32_t* out);
+/* matrix.h:557-567 DenseMatrix::sync2gpu(segment): split of the leading dimension. */
+SBLAS_API int sblas_dense_split_i32(int32_t first_order, unsigned n_gpu, int32_t* avg_val,
+                                    int32_t* dim_gpu);
+/* nnz-balanced ROW-ALIGNED panels (north star, method 2): panel i = rows
+ * [row_begin[i], row_begin[i+1]); row_begin has n_gpu+1 entries.  A row belongs to the
+ * panel in which the reference's nnz split puts its first nnz. */
+SBLAS_API int sblas_csr_partition_rows_i32(const int32_t* rowptr, int32_t height, unsigned n_gpu,
+                                           int32_t* row_begin);
+
+/* ---- Matrix Market loader (mmio_highlevel.h:7-127, :130-281; matrix.h:300-318) ------- */
+SBLAS_API int sblas_mtx_info(const char* filename, int32_t* m, int32_t* n, int32_t* nnz,
+                             int32_t* is_symmetric);
+SBLAS_API int sblas_mtx_data(const char* filename, int32_t* rowptr, int32_t* colidx, double* val);
+
+/* ---- per-device CSR plan (tile tables + row statistics; built once at sync2gpu) ------ */
+typedef struct sblasPlan_st* sblasPlan_t;
+typedef struct sblasCsrStats {
+  int64_t nnz;
+  int32_t rows;
+  int32_t max_row_nnz;
+  int32_t empty_rows;
+  int32_t spmv_variant; /* what AUTO resolves to */
+  int32_t spmv_tile, spmv_tiles, spmv_smem_bytes;
+  int32_t spmm_tile, spmm_tiles;
+} sblasCsrStats;
+SBLAS_API int sblas_plan_create_i32(void* stream, int32_t rows, int64_t nnz,
+                                    const int32_t* d_rowptr, sblasPlan_t* plan);
+SBLAS_API int sblas_plan_stats(sblasPlan_t plan, sblasCsrStats* out);
+SBLAS_API int sblas_plan_destroy(sblasPlan_t plan);
+
+/* ---- single-device kernels ---------------------------------------------------------- */
+/* y <- beta*y + alpha*A*x on the current device.  Replaces cusparseSpMV at spmv.h:96-106
+ * plus the axpby pass of spmv.h:138 / kernel.h:28-37 (fused into the epilogue).
+ * plan may be NULL (an internal plan is then built and dropped on every call). */
+SBLAS_API int sblas_spmv_csr_f64(void* stream, int32_t rows, int32_t cols, int64_t nnz,
+                                 const int32_t* d_rowptr, const int32_t* d_colidx,
+                                 const double* d_val, const double* d_x, double* d_y, double alpha,
+                                 double beta, sblasPlan_t plan, const sblasOpts* opts);
+SBLAS_API int sblas_spmv_csr_f32(void* stream, int32_t rows, int32_t cols, int64_t nnz,
+                                 const int32_t* d_rowptr, const int32_t* d_colidx,
+                                 const float* d_val, const float* d_x, float* d_y, float alpha,
+                                 float beta, sblasPlan_t plan, const sblasOpts* opts);
+
+/* C <- beta*C + alpha*A*B on the current device, k dense columns.  Replaces cusparseSpMM
+ * at spmm.h:135-149 (method 1) / :240-251 (method 2) plus the axpby of spmm.h:283.
+ * layout = SBLAS_ROW_MAJOR: B[c*ldb + n], C[r*ldc + n] (the internal device layout);
+ * layout = SBLAS_COL_MAJOR: B[n*ldb + c], C[n*ldc + r] (the reference's layout, spmm.h:121-132). */
+SBLAS_API int sblas_spmm_csr_f64(void* stream, int32_t rows, int32_t cols, int64_t nnz,
+                                 const int32_t* d_rowptr, const int32_t* d_colidx,
+                                 const double* d_val, int32_t k, int32_t layout, const double* d_B,
+                                 int64_t ldb, double* d_C, int64_t ldc, double alpha, double beta,
+                                 sblasPlan_t plan, const sblasOpts* opts);
+SBLAS_API int sblas_spmm_csr_f32(void* stream, int32_t rows, int32_t cols, int64_t nnz,
+                                 const int32_t* d_rowptr, const int32_t* d_colidx,
+                                 const float* d_val, int32_t k, int32_t layout, const float* d_B,
+                                 int64_t ldb, float* d_C, int64_t ldc, float alpha, float beta,
+                                 sblasPlan_t plan, const sblasOpts* opts);
+
+/* kernel.h:28-37 denseVector_plusEqual_denseVector: v0[i] = v0[i]*beta + v1[i]*alpha. */
+SBLAS_API int sblas_axpby_f64(void* stream, double* d_v0, const double* d_v1, double alpha,
+                              double beta, int64_t n);
+SBLAS_API int sblas_axpby_f32(void* stream, float* d_v0, const float* d_v1, float alpha,
+                              float beta, int64_t n);
+/* kernel.h:19-25 denseVector_plusEqual_scalar (with the index bug at :22 fixed):
+ * v[i] = v[i]*beta + val. */
+SBLAS_API int sblas_scal_add_f64(void* stream, double* d_v, double val, double beta, int64_t n);
+SBLAS_API int sblas_scal_add_f32(void* stream, float* d_v, float val, float beta, int64_t n);
+
+/* out[b*out_ld + a] = in[a*in_ld + b], a < n_major, b < n_minor.  Converts the reference's
+ * col-major dense operands (matrix.h:37) to the internal row-major device layout and back
+ * (inside DenseMatrix::sync2gpu / sync2cpu, matrix.h:541-570, :595-612). */
+SBLAS_API int sblas_transpose_f64(void* stream, const double* d_in, int64_t in_ld, int64_t n_major,
+                                  int64_t n_minor, double* d_out, int64_t out_ld);
+SBLAS_API int sblas_transpose_f32(void* stream, const float* d_in, int64_t in_ld, int64_t n_major,
+                                  int64_t n_minor, float* d_out, int64_t out_ld);
+
+/* ---- multi-GPU ops, one process driving GPUs 0..n_gpu-1 (the reference's execution model:
+ *      spmv.h:52-55, spmm.h:101-104; streams/events/peer access live in a cached context) ---- */
+
+/* sblas_spmv_csr_v1, spmv.h:36-139.  A nnz-segmented exactly as matrix.h:356-394 leaves it
+ * (per-GPU local rowptr / col / val slices and the three partition tables); x and y
+ * replicated.  On return EVERY replica y_gpu[i] holds beta*y + alpha*A*x (the reference's
+ * post-condition, matrix.h:714-726).  Owner-computes rows + direct peer stores from the
+ * kernel epilogue replace the reference's zero-buffer + ncclAllReduce + axpby passes; rows
+ * shared by neighbouring GPUs are finished by a carry fix-up.  plans[i] may be NULL. */
+SBLAS_API int sblas_mgpu_spmv_csr_v1_f64(unsigned n_gpu, int32_t height, int32_t width,
+                                         const int32_t* const* rowptr_gpu,
+                                         const int32_t* const* colidx_gpu,
+                                         const double* const* val_gpu, const int32_t* nnz_gpu,
+                                         const int32_t* starting_row_gpu,
+                                         const int32_t* stoping_row_gpu,
+                                         const double* const* x_gpu, double* const* y_gpu,
+                                         double alpha, double beta, const sblasPlan_t* plans);
+SBLAS_API int sblas_mgpu_spmv_csr_v1_f32(unsigned n_gpu, int32_t height, int32_t width,
+                                         const int32_t* const* rowptr_gpu,
+                                         const int32_t* const* colidx_gpu,
+                                         const float* const* val_gpu, const int32_t* nnz_gpu,
+                                         const int32_t* starting_row_gpu,
+                                         const int32_t* stoping_row_gpu,
+                                         const float* const* x_gpu, float* const* y_gpu,
+                                         float alpha, float beta, const sblasPlan_t* plans);
+
+/* sblas_spmm_csr_v1 (method 1), spmm.h:84-161: A replicated, B and C split by columns
+ * (dim_gpu[i] columns on GPU i, matrix.h:557-567).  No inter-GPU traffic.  layout/ld as in
+ * sblas_spmm_csr_*; ldb/ldc arrays have one entry per GPU. */
+SBLAS_API int sblas_mgpu_spmm_csr_v1_f64(unsigned n_gpu, int32_t height, int32_t width,
+                                         int32_t nnz, const int32_t* const* rowptr_gpu,
+                                         const int32_t* const* colidx_gpu,
+                                         const double* const* val_gpu, const int32_t* dim_gpu,
+                                         int32_t layout, const double* const* B_gpu,
+                                         const int64_t* ldb, double* const* C_gpu,
+                                         const int64_t* ldc, double alpha, double beta,
+                                         const sblasPlan_t* plans);
+SBLAS_API int sblas_mgpu_spmm_csr_v1_f32(unsigned n_gpu, int32_t height, int32_t width,
+                                         int32_t nnz, const int32_t* const* rowptr_gpu,
+                                         const int32_t* const* colidx_gpu,
+                                         const float* const* val_gpu, const int32_t* dim_gpu,
+                                         int32_t layout, const float* const* B_gpu,
+                                         const int64_t* ldb, float* const* C_gpu,
+                                         const int64_t* ldc, float alpha, float beta,
+                                         const sblasPlan_t* plans);
+
+/* sblas_spmm_csr_v2 (method 2), spmm.h:164-284: A nnz-segmented, B and C replicated.  On
+ * return every replica C_gpu[i] holds beta*C + alpha*A*B.  Same owner-computes + peer-store
+ * stitch as the SpMV above (replaces C_copy + ncclAllReduce(h*k) + axpby, spmm.h:182,260,283). */
+SBLAS_API int sblas_mgpu_spmm_csr_v2_f64(unsigned n_gpu, int32_t height, int32_t width,
+                                         const int32_t* const* rowptr_gpu,
+                                         const int32_t* const* colidx_gpu,
+                                         const double* const* val_gpu, const int32_t* nnz_gpu,
+                                         const int32_t* starting_row_gpu,
+                                         const int32_t* stoping_row_gpu, int32_t k, int32_t layout,
+                                         const double* const* B_gpu, int64_t ldb,
+                                         double* const* C_gpu, int64_t ldc, double alpha,
+                                         double beta, const sblasPlan_t* plans);
+SBLAS_API int sblas_mgpu_spmm_csr_v2_f32(unsigned n_gpu, int32_t height, int32_t width,
+                                         const int32_t* const* rowptr_gpu,
+                                         const int32_t* const* colidx_gpu,
+                                         const float* const* val_gpu, const int32_t* nnz_gpu,
+                                         const int32_t* starting_row_gpu,
+                                         const int32_t* stoping_row_gpu, int32_t k, int32_t layout,
+                                         const float* const* B_gpu, int64_t ldb,
+                                         float* const* C_gpu, int64_t ldc, float alpha,
+                                         float beta, const sblasPlan_t* plans);
+
+/* Carry fix-up for rows shared between neighbouring segments (used by the multi-process
+ * path too): for each of the n_shared rows, out[row] = beta*out[row] + alpha*sum(carries),
+ * carries added in GPU order.  carry holds n_gpu*2*k values ([gpu][head|tail][k]),
+ * rows/first/last have n_shared entries: the row index and the first/last contributing GPU. */
+SBLAS_API int sblas_carry_fixup_f64(void* stream, int32_t n_shared, const int32_t* h_rows,
+                                    const int32_t* h_first_gpu, const int32_t* h_last_gpu,
+                                    const double* d_carry, int32_t k, int32_t layout, double* d_out,
+                                    int64_t ld, double alpha, double beta);
+SBLAS_API int sblas_carry_fixup_f32(void* stream, int32_t n_shared, const int32_t* h_rows,
+                                    const int32_t* h_first_gpu, const int32_t* h_last_gpu,
+                                    const float* d_carry, int32_t k, int32_t layout, float* d_out,
+                                    int64_t ld, float alpha, float beta);
+
+/* ---- synthetic inputs of BASELINE.json's configs, generated on the device --------------
+ * (replace matrices/get_matrices.sh:4-5, which needs the network).  All generators are
+ * counter-based (splitmix64 keyed by seed and element index) and are restated in numpy in
+ * tests/synth_ref.py; the tests check the two bit for bit. */
+/* p[i] = lo + (hi-lo)*u01(seed, stream_id, i) */
+SBLAS_API int sblas_synth_fill_f64(void* stream, double* d_p, int64_t n, uint64_t seed,
+                                   uint64_t stream_id, double lo, double hi);
+SBLAS_API int sblas_synth_fill_f32(void* stream, float* d_p, int64_t n, uint64_t seed,
+                                   uint64_t stream_id, float lo, float hi);
+/* 2-D 5-point Laplacian, nx*ny rows, Dirichlet, columns ascending; nnz = 5*nx*ny-2*nx-2*ny.
+ * d_val may be f32 or f64 (val_is_f64). */
+SBLAS_API int64_t sblas_synth_laplace2d_nnz(int32_t nx, int32_t ny);
+SBLAS_API int sblas_synth_laplace2d(void* stream, int32_t nx, int32_t ny, int32_t* d_rowptr,
+                                    int32_t* d_colidx, void* d_val, int val_is_f64);
+/* rows x cols, exactly `deg` distinct uniform columns per row (sorted), values in [-1,1). */
+SBLAS_API int sblas_synth_uniform(void* stream, int32_t rows, int32_t cols, int32_t deg,
+                                  uint64_t seed, int32_t* d_rowptr, int32_t* d_colidx,
+                                  void* d_val, int val_is_f64);
+/* banded: row i holds the `bw` consecutive columns starting at clamp(i-bw/2, 0, n-bw). */
+SBLAS_API int sblas_synth_banded(void* stream, int32_t n, int32_t bw, uint64_t seed,
+                                 int32_t* d_rowptr, int32_t* d_colidx, void* d_val,
+                                 int val_is_f64);
+/* R-MAT (a,b,c,d = .57,.19,.19,.05), 2^scale rows, edge_factor*2^scale edges, duplicates
+ * merged (values summed), columns sorted.  Two calls: the first (d_colidx == NULL) returns
+ * the merged nnz in *nnz_out and keeps the edges in a device scratch owned by the library;
+ * the second fills the three arrays and frees the scratch. */
+SBLAS_API int sblas_synth_rmat(void* stream, int32_t scale, int32_t edge_factor, uint64_t seed,
+                               int64_t* nnz_out, int32_t* d_rowptr, int32_t* d_colidx,
+                               void* d_val, int val_is_f64);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SBLAS_B200_H */

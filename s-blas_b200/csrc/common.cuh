@@ -1,0 +1,149 @@
+// common.cuh — shared device/host helpers for libsblas_b200.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+
+#include "sblas_b200.h"
+
+namespace sblas {
+
+// ---- error plumbing -------------------------------------------------------------------
+// The reference prints and exit(-1)s on any CUDA failure (utility.h:27-83).  The C ABI
+// returns a code and keeps the message; the C++ drop-in headers turn it back into
+// print-and-exit.
+void set_error(const char* fmt, ...);
+const char* get_error();
+
+#define SBLAS_CUDA(call)                                                                   \
+  do {                                                                                     \
+    cudaError_t e__ = (call);                                                              \
+    if (e__ != cudaSuccess) {                                                              \
+      ::sblas::set_error("%s failed at %s:%d : %s", #call, __FILE__, __LINE__,             \
+                         cudaGetErrorString(e__));                                         \
+      return 1;                                                                            \
+    }                                                                                      \
+  } while (0)
+
+#define SBLAS_CHECK(cond, ...)                                                             \
+  do {                                                                                     \
+    if (!(cond)) {                                                                         \
+      ::sblas::set_error(__VA_ARGS__);                                                     \
+      return 2;                                                                            \
+    }                                                                                      \
+  } while (0)
+
+#define SBLAS_LAUNCH_CHECK()                                                               \
+  do {                                                                                     \
+    cudaError_t e__ = cudaGetLastError();                                                  \
+    if (e__ != cudaSuccess) {                                                              \
+      ::sblas::set_error("kernel launch failed at %s:%d : %s", __FILE__, __LINE__,         \
+                         cudaGetErrorString(e__));                                         \
+      return 3;                                                                            \
+    }                                                                                      \
+  } while (0)
+
+constexpr int kNumSM = 148;  // B200: 2 dies x 74 SMs
+
+// ---- output replicas (fused stitch: the epilogue stores every result to the local y/C
+//      and to the same offset of each peer GPU's replica over NVLink) -------------------
+template <typename T>
+struct OutSpec {
+  int n;                        // number of extra replicas
+  T* ptr[SBLAS_MAX_GPU - 1];
+};
+
+template <typename T>
+inline OutSpec<T> make_outspec(const sblasOpts* o) {
+  OutSpec<T> s;
+  s.n = 0;
+  for (int i = 0; i < SBLAS_MAX_GPU - 1; ++i) s.ptr[i] = nullptr;
+  if (o) {
+    s.n = o->n_replica;
+    for (int i = 0; i < o->n_replica && i < SBLAS_MAX_GPU - 1; ++i) s.ptr[i] = (T*)o->replica[i];
+  }
+  return s;
+}
+
+// ---- exactly rounded arithmetic ---------------------------------------------------------
+// The reference's CPU loops (spmv.h:26-30, spmm.h:60-66) run as separately rounded
+// multiply and add on x86-64 (no FMA in its build flags, Makefile:23).  The sequential
+// kernel paths use these so that their results are bit-identical to it; nvcc would
+// otherwise contract a*b+c into an FMA.
+__device__ __forceinline__ double mul_rn(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ float mul_rn(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ double add_rn(double a, double b) { return __dadd_rn(a, b); }
+__device__ __forceinline__ float add_rn(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ double fma_rn(double a, double b, double c) { return __fma_rn(a, b, c); }
+__device__ __forceinline__ float fma_rn(float a, float b, float c) { return __fmaf_rn(a, b, c); }
+
+// beta*y + alpha*s exactly as `beta * (pC->val[i]) + alpha * sum` (spmv.h:31, spmm.h:66).
+template <typename T>
+__device__ __forceinline__ T axpby_rn(T alpha, T s, T beta, T y) {
+  return add_rn(mul_rn(beta, y), mul_rn(alpha, s));
+}
+
+// ---- loads with cache hints ------------------------------------------------------------
+// Streaming (touched once) operands: col_idx / val of A.  Bypass L1 so the gathered
+// x / B lines keep it.
+__device__ __forceinline__ int4 ldg_stream_i4(const int4* p) {
+  int4 r;
+  asm("ld.global.nc.L1::no_allocate.v4.s32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ double2 ldg_stream_d2(const double2* p) {
+  double2 r;
+  asm("ld.global.nc.L1::no_allocate.v2.f64 {%0,%1}, [%2];" : "=d"(r.x), "=d"(r.y) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ float4 ldg_stream_f4(const float4* p) {
+  float4 r;
+  asm("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ int ldg_stream(const int* p) {
+  int r;
+  asm("ld.global.nc.L1::no_allocate.s32 %0, [%1];" : "=r"(r) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ double ldg_stream(const double* p) {
+  double r;
+  asm("ld.global.nc.L1::no_allocate.f64 %0, [%1];" : "=d"(r) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ float ldg_stream(const float* p) {
+  float r;
+  asm("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(r) : "l"(p));
+  return r;
+}
+
+// 16-byte vector type of T
+template <typename T> struct Vec16;
+template <> struct Vec16<double> { using type = double2; static constexpr int N = 2; };
+template <> struct Vec16<float> { using type = float4; static constexpr int N = 4; };
+
+__device__ __forceinline__ double2 ldg_v(const double2* p) { return __ldg(p); }
+__device__ __forceinline__ float4 ldg_v(const float4* p) { return __ldg(p); }
+__device__ __forceinline__ double2 ldg_v_nol1(const double2* p) { return ldg_stream_d2(p); }
+__device__ __forceinline__ float4 ldg_v_nol1(const float4* p) { return ldg_stream_f4(p); }
+
+template <typename T>
+__device__ __forceinline__ T warp_max(T v) {
+#pragma unroll
+  for (int m = 16; m > 0; m >>= 1) {
+    T o = __shfl_xor_sync(0xffffffffu, v, m);
+    v = o > v ? o : v;
+  }
+  return v;
+}
+
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
+
+}  // namespace sblas

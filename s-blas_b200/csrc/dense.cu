@@ -1,0 +1,127 @@
+// dense.cu — element-wise utility kernels and the col-major <-> row-major converter.
+//
+// kernel.h:28-37 denseVector_plusEqual_denseVector and kernel.h:19-25
+// denseVector_plusEqual_scalar of the reference, vectorised (128-bit) with a grid sized to
+// the SM count; the hot path itself fuses the axpby into the SpMV/SpMM epilogues and only
+// keeps these for API parity (DenseVector::plusDenseVectorGPU, matrix.h:714-726).
+#include "common.cuh"
+
+namespace sblas {
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+axpby_kernel(T* __restrict__ v0, const T* __restrict__ v1, T alpha, T beta, int64_t n, bool vec) {
+  using V = typename Vec16<T>::type;
+  constexpr int N = Vec16<T>::N;
+  const int64_t tid = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  const int64_t nth = (int64_t)gridDim.x * blockDim.x;
+  int64_t done = 0;
+  if (vec) {
+    const int64_t nv = n / N;
+    for (int64_t i = tid; i < nv; i += nth) {
+      V a = reinterpret_cast<V*>(v0)[i];
+      const V b = __ldg(reinterpret_cast<const V*>(v1) + i);
+      T* pa = reinterpret_cast<T*>(&a);
+      const T* pb = reinterpret_cast<const T*>(&b);
+#pragma unroll
+      for (int e = 0; e < N; ++e) pa[e] = add_rn(mul_rn(pa[e], beta), mul_rn(pb[e], alpha));  // kernel.h:34
+      reinterpret_cast<V*>(v0)[i] = a;
+    }
+    done = nv * N;
+  }
+  for (int64_t i = done + tid; i < n; i += nth)
+    v0[i] = add_rn(mul_rn(v0[i], beta), mul_rn(v1[i], alpha));
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+scal_add_kernel(T* __restrict__ v, T val, T beta, int64_t n) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x)
+    v[i] = add_rn(mul_rn(v[i], beta), val);  // kernel.h:24 with the :22 index bug fixed
+}
+
+// out[b*out_ld + a] = in[a*in_ld + b]; 32x32 tiles through shared memory (+1 padding), both
+// sides coalesced.  Grid-stride over tiles so any size fits a grid of a few waves.
+template <typename T>
+__global__ void __launch_bounds__(256)
+transpose_kernel(const T* __restrict__ in, int64_t in_ld, int64_t n_major, int64_t n_minor,
+                 T* __restrict__ out, int64_t out_ld) {
+  __shared__ T tile[32][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+  const int64_t tiles_b = (n_minor + 31) / 32, tiles_a = (n_major + 31) / 32;
+  const int64_t ntiles = tiles_a * tiles_b;
+  for (int64_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
+    const int64_t ta = t / tiles_b, tb = t % tiles_b;
+#pragma unroll
+    for (int i = 0; i < 32; i += 8) {
+      const int64_t a = ta * 32 + ty + i, b = tb * 32 + tx;
+      if (a < n_major && b < n_minor) tile[ty + i][tx] = in[a * in_ld + b];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < 32; i += 8) {
+      const int64_t b = tb * 32 + ty + i, a = ta * 32 + tx;
+      if (a < n_major && b < n_minor) out[b * out_ld + a] = tile[tx][ty + i];
+    }
+    __syncthreads();
+  }
+}
+
+template <typename T>
+static int axpby_impl(cudaStream_t st, T* v0, const T* v1, T alpha, T beta, int64_t n) {
+  if (n <= 0) return 0;
+  SBLAS_CHECK(v0 && v1, "axpby: null pointer");
+  const int64_t per = 256 * (int64_t)Vec16<T>::N;
+  const int blocks = (int)std::min<int64_t>(ceil_div(n, per), kNumSM * 16);
+  axpby_kernel<T><<<blocks, 256, 0, st>>>(v0, v1, alpha, beta, n, aligned16(v0) && aligned16(v1));
+  SBLAS_LAUNCH_CHECK();
+  return 0;
+}
+template <typename T>
+static int scal_add_impl(cudaStream_t st, T* v, T val, T beta, int64_t n) {
+  if (n <= 0) return 0;
+  SBLAS_CHECK(v, "scal_add: null pointer");
+  const int blocks = (int)std::min<int64_t>(ceil_div(n, 256), kNumSM * 16);
+  scal_add_kernel<T><<<blocks, 256, 0, st>>>(v, val, beta, n);
+  SBLAS_LAUNCH_CHECK();
+  return 0;
+}
+template <typename T>
+static int transpose_impl(cudaStream_t st, const T* in, int64_t in_ld, int64_t n_major,
+                          int64_t n_minor, T* out, int64_t out_ld) {
+  if (n_major <= 0 || n_minor <= 0) return 0;
+  SBLAS_CHECK(in && out && in != out, "transpose: bad pointers (must be out of place)");
+  SBLAS_CHECK(in_ld >= n_minor && out_ld >= n_major, "transpose: leading dimension too small");
+  const int64_t ntiles = ceil_div(n_major, 32) * ceil_div(n_minor, 32);
+  const int blocks = (int)std::min<int64_t>(ntiles, kNumSM * 32);
+  transpose_kernel<T><<<blocks, 256, 0, st>>>(in, in_ld, n_major, n_minor, out, out_ld);
+  SBLAS_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // namespace sblas
+
+using namespace sblas;
+extern "C" {
+int sblas_axpby_f64(void* s, double* v0, const double* v1, double a, double b, int64_t n) {
+  return axpby_impl<double>((cudaStream_t)s, v0, v1, a, b, n);
+}
+int sblas_axpby_f32(void* s, float* v0, const float* v1, float a, float b, int64_t n) {
+  return axpby_impl<float>((cudaStream_t)s, v0, v1, a, b, n);
+}
+int sblas_scal_add_f64(void* s, double* v, double val, double beta, int64_t n) {
+  return scal_add_impl<double>((cudaStream_t)s, v, val, beta, n);
+}
+int sblas_scal_add_f32(void* s, float* v, float val, float beta, int64_t n) {
+  return scal_add_impl<float>((cudaStream_t)s, v, val, beta, n);
+}
+int sblas_transpose_f64(void* s, const double* in, int64_t in_ld, int64_t n_major, int64_t n_minor,
+                        double* out, int64_t out_ld) {
+  return transpose_impl<double>((cudaStream_t)s, in, in_ld, n_major, n_minor, out, out_ld);
+}
+int sblas_transpose_f32(void* s, const float* in, int64_t in_ld, int64_t n_major, int64_t n_minor,
+                        float* out, int64_t out_ld) {
+  return transpose_impl<float>((cudaStream_t)s, in, in_ld, n_major, n_minor, out, out_ld);
+}
+}
