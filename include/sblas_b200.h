@@ -41,6 +41,8 @@ SBLAS_API int sblas_version(void);
 SBLAS_API const char* sblas_last_error(void);
 /* number of visible CUDA devices (0 when there is no driver/GPU) */
 SBLAS_API int sblas_device_count(void);
+/* number of CUDA kernels this library has launched so far in this process */
+SBLAS_API unsigned long long sblas_launch_count(void);
 
 /* ---- launch options ------------------------------------------------------------ */
 enum {
@@ -70,7 +72,8 @@ typedef struct sblasOpts {
   int32_t n_replica; /* extra copies of the output to store (peer GPUs' replicas), <= 15 */
   int32_t reserved;
   void* replica[SBLAS_MAX_GPU - 1]; /* same logical base pointer as y / C on each peer */
-  void* carry;       /* device buffer of 2*k DataType for HEAD/TAIL partial sums */
+  void* carry;       /* device buffer of 2*((k+3)&~3) DataType: HEAD sums at [0,k), TAIL sums at
+                        [(k+3)&~3, ...) (k = 1 for SpMV) */
 } sblasOpts;
 
 /* ---- integer layer: partitioners (host, bit-exact with the reference) ------------- */
@@ -167,6 +170,11 @@ SBLAS_API int sblas_transpose_f32(void* stream, const float* d_in, int64_t in_ld
 /* ---- multi-GPU ops, one process driving GPUs 0..n_gpu-1 (the reference's execution model:
  *      spmv.h:52-55, spmm.h:101-104; streams/events/peer access live in a cached context) ---- */
 
+/* Physical CUDA device of logical GPU i.  Identity (the reference's cudaSetDevice(i_gpu),
+ * spmv.h:55) unless the environment variable SBLAS_DEVICE_MAP="d0,d1,..." remaps it, which
+ * lets an n-way partition run on fewer devices (several logical GPUs per device). */
+SBLAS_API int sblas_device_of(int logical_gpu);
+
 /* sblas_spmv_csr_v1, spmv.h:36-139.  A nnz-segmented exactly as matrix.h:356-394 leaves it
  * (per-GPU local rowptr / col / val slices and the three partition tables); x and y
  * replicated.  On return EVERY replica y_gpu[i] holds beta*y + alpha*A*x (the reference's
@@ -231,6 +239,15 @@ SBLAS_API int sblas_mgpu_spmm_csr_v2_f32(unsigned n_gpu, int32_t height, int32_t
                                          const float* const* B_gpu, int64_t ldb,
                                          float* const* C_gpu, int64_t ldc, float alpha,
                                          float beta, const sblasPlan_t* plans);
+
+/* One process per GPU (torch.distributed / MPI style launch): replicas that every rank of the
+ * node can store into.  ipc_alloc = cudaMalloc + cudaIpcGetMemHandle (64-byte handle to ship to
+ * the peers), ipc_open maps a peer's buffer; the mapped pointers go into sblasOpts.replica so
+ * the SpMV/SpMM epilogue writes every finished row into all replicas over NVLink. */
+SBLAS_API int sblas_ipc_alloc(size_t bytes, void** d_ptr, unsigned char handle[64]);
+SBLAS_API int sblas_ipc_open(const unsigned char handle[64], void** d_ptr);
+SBLAS_API int sblas_ipc_close(void* d_ptr);
+SBLAS_API int sblas_ipc_free(void* d_ptr);
 
 /* Carry fix-up for rows shared between neighbouring segments (used by the multi-process
  * path too): for each of the n_shared rows, out[row] = beta*out[row] + alpha*sum(carries),

@@ -12,7 +12,7 @@ Layout:
   dist.py      one-process-per-GPU variants over torch.distributed
   synth.py     device-side synthetic inputs of BASELINE.json's configs
 """
-from . import _lib, kernels, matrix, ops, synth  # noqa: F401
+from . import _lib, dist, kernels, matrix, ops, synth, synth_np  # noqa: F401
 from ._lib import (COL_MAJOR, FLAG_FMA, FLAG_HEAD_PARTIAL, FLAG_NO_L1, FLAG_TAIL_PARTIAL,  # noqa: F401
                    ROW_MAJOR, SPMM_COLMAJOR, SPMM_ROWMAJOR, SPMV_SPLIT, SPMV_TILE, SPMV_VECTOR,
                    SblasError, make_opts)

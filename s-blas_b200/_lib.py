@@ -47,6 +47,7 @@ def lib():
         _lib.sblas_last_error.restype = C.c_char_p
         _lib.sblas_synth_laplace2d_nnz.restype = C.c_int64
         _lib.sblas_csr_find_row_i32.restype = C.c_int32
+        _lib.sblas_launch_count.restype = C.c_ulonglong
     return _lib
 
 

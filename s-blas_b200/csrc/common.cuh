@@ -34,8 +34,11 @@ const char* get_error();
     }                                                                                      \
   } while (0)
 
+// every kernel launch of the library is counted (bench.py reports it as gpu_launches)
+extern unsigned long long g_launches;
 #define SBLAS_LAUNCH_CHECK()                                                               \
   do {                                                                                     \
+    ++::sblas::g_launches;                                                                 \
     cudaError_t e__ = cudaGetLastError();                                                  \
     if (e__ != cudaSuccess) {                                                              \
       ::sblas::set_error("kernel launch failed at %s:%d : %s", __FILE__, __LINE__,         \

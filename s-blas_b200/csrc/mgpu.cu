@@ -65,6 +65,27 @@ static int launch_finish(cudaStream_t st, const FinishList& fl, const T* carry, 
   return 0;
 }
 
+// ---- logical GPU -> physical device ------------------------------------------------------------
+// SBLAS_DEVICE_MAP="0,0,1,1" runs a 4-way partition on two physical devices (several logical
+// GPUs may share one device: their kernels then simply run back to back on its default
+// stream).  Default: identity, i.e. the reference's cudaSetDevice(i_gpu) (spmv.h:55).
+static int g_devmap[SBLAS_MAX_GPU];
+static bool g_devmap_init = false;
+static int device_of(int i) {
+  if (!g_devmap_init) {
+    for (int j = 0; j < SBLAS_MAX_GPU; ++j) g_devmap[j] = j;
+    if (const char* e = getenv("SBLAS_DEVICE_MAP")) {
+      int j = 0;
+      while (*e && j < SBLAS_MAX_GPU) {
+        g_devmap[j++] = (int)strtol(e, (char**)&e, 10);
+        while (*e == ',' || *e == ' ') ++e;
+      }
+    }
+    g_devmap_init = true;
+  }
+  return (i >= 0 && i < SBLAS_MAX_GPU) ? g_devmap[i] : i;
+}
+
 // ---- cached context -----------------------------------------------------------------------------
 struct MgpuCtx {
   int n = 0;
@@ -79,19 +100,20 @@ static int ctx_get(unsigned n_gpu, size_t carry_bytes, MgpuCtx** out) {
   SBLAS_CHECK(n_gpu >= 1 && n_gpu <= SBLAS_MAX_GPU, "n_gpu must be in 1..%d", SBLAS_MAX_GPU);
   int ndev = 0;
   SBLAS_CUDA(cudaGetDeviceCount(&ndev));
-  SBLAS_CHECK((int)n_gpu <= ndev, "n_gpu=%u but only %d CUDA devices are visible", n_gpu, ndev);
+  for (unsigned i = 0; i < n_gpu; ++i)
+    SBLAS_CHECK(device_of(i) < ndev, "logical GPU %u maps to device %d but only %d CUDA devices are visible", i, device_of(i), ndev);
   int cur = 0;
   SBLAS_CUDA(cudaGetDevice(&cur));
   if (g_ctx.n < (int)n_gpu) {
     bool ok = true;
     for (unsigned i = 0; i < n_gpu; ++i) {
-      SBLAS_CUDA(cudaSetDevice(i));
+      SBLAS_CUDA(cudaSetDevice(device_of(i)));
       for (unsigned j = 0; j < n_gpu; ++j) {
-        if (i == j) continue;
+        if (device_of(i) == device_of(j)) continue;
         int can = 0;
-        SBLAS_CUDA(cudaDeviceCanAccessPeer(&can, i, j));
+        SBLAS_CUDA(cudaDeviceCanAccessPeer(&can, device_of(i), device_of(j)));
         if (!can) { ok = false; continue; }
-        cudaError_t e = cudaDeviceEnablePeerAccess(j, 0);
+        cudaError_t e = cudaDeviceEnablePeerAccess(device_of(j), 0);
         if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
         else if (e != cudaSuccess) { cudaGetLastError(); ok = false; }
       }
@@ -102,12 +124,12 @@ static int ctx_get(unsigned n_gpu, size_t carry_bytes, MgpuCtx** out) {
   }
   if (g_ctx.carry_bytes < carry_bytes) {
     for (int i = 0; i < SBLAS_MAX_GPU; ++i)
-      if (g_ctx.carry[i]) { cudaSetDevice(i); cudaFree(g_ctx.carry[i]); g_ctx.carry[i] = nullptr; }
+      if (g_ctx.carry[i]) { cudaSetDevice(device_of(i)); cudaFree(g_ctx.carry[i]); g_ctx.carry[i] = nullptr; }
     g_ctx.carry_bytes = 0;
   }
   for (unsigned i = 0; i < n_gpu; ++i)
     if (!g_ctx.carry[i]) {
-      SBLAS_CUDA(cudaSetDevice(i));
+      SBLAS_CUDA(cudaSetDevice(device_of(i)));
       SBLAS_CUDA(cudaMalloc(&g_ctx.carry[i], std::max<size_t>(carry_bytes, 4096)));
     }
   g_ctx.carry_bytes = std::max<size_t>(std::max<size_t>(carry_bytes, 4096), g_ctx.carry_bytes);
@@ -165,7 +187,7 @@ static int mgpu_rowsplit(unsigned n_gpu, int32_t height, int32_t width,
   // 1. every GPU: its segment, fused epilogue, stores into all replicas
   for (unsigned i = 0; i < n_gpu && rc == 0; ++i) {
     if (!active[i]) continue;
-    SBLAS_CUDA(cudaSetDevice(i));
+    SBLAS_CUDA(cudaSetDevice(device_of(i)));
     const int32_t rows = erow[i] - srow[i] + 1;
     sblasOpts o;
     memset(&o, 0, sizeof o);
@@ -191,7 +213,7 @@ static int mgpu_rowsplit(unsigned n_gpu, int32_t height, int32_t width,
     if (head[i] || tail[i])
       for (unsigned d = 0; d < n_gpu; ++d)
         if (d != i)
-          SBLAS_CUDA(cudaMemcpyPeerAsync((T*)ctx->carry[d] + (size_t)i * 2 * kpad, d, carry_i, i,
+          SBLAS_CUDA(cudaMemcpyPeerAsync((T*)ctx->carry[d] + (size_t)i * 2 * kpad, device_of(d), carry_i, device_of(i),
                                          sizeof(T) * 2 * kpad, nullptr));
     // without peer stores: ship the finished panel to the other replicas
     if (!peer && n_gpu > 1) {
@@ -199,10 +221,10 @@ static int mgpu_rowsplit(unsigned n_gpu, int32_t height, int32_t width,
         if (d == i) continue;
         if (!is_spmm || layout == SBLAS_ROW_MAJOR) {
           const size_t bytes = sizeof(T) * (is_spmm ? (size_t)rows * ldc : (size_t)rows);
-          SBLAS_CUDA(cudaMemcpyPeerAsync(C[d] + row_off, d, C[i] + row_off, i, bytes, nullptr));
+          SBLAS_CUDA(cudaMemcpyPeerAsync(C[d] + row_off, device_of(d), C[i] + row_off, device_of(i), bytes, nullptr));
         } else {
           for (int32_t n = 0; n < k; ++n)
-            SBLAS_CUDA(cudaMemcpyPeerAsync(C[d] + row_off + (int64_t)n * ldc, d, C[i] + row_off + (int64_t)n * ldc, i, sizeof(T) * rows, nullptr));
+            SBLAS_CUDA(cudaMemcpyPeerAsync(C[d] + row_off + (int64_t)n * ldc, device_of(d), C[i] + row_off + (int64_t)n * ldc, device_of(i), sizeof(T) * rows, nullptr));
         }
       }
     }
@@ -212,13 +234,13 @@ static int mgpu_rowsplit(unsigned n_gpu, int32_t height, int32_t width,
   //    and the uncovered rows of its own replica.  Step 1 never writes those rows with new
   //    values (a panel copy can only carry their old value), so running this last is enough.
   for (unsigned d = 0; d < n_gpu && rc == 0; ++d) {
-    SBLAS_CUDA(cudaSetDevice(d));
+    SBLAS_CUDA(cudaSetDevice(device_of(d)));
     for (unsigned i = 0; i < n_gpu; ++i)
       if (i != d && active[i]) SBLAS_CUDA(cudaStreamWaitEvent(nullptr, ctx->ev[i], 0));
     rc = launch_finish<T>(nullptr, fl, (const T*)ctx->carry[d], kpad, k, layout, C[d], ldc, alpha, beta);
   }
   for (unsigned d = 0; d < n_gpu; ++d) {
-    cudaSetDevice(d);
+    cudaSetDevice(device_of(d));
     cudaError_t e = cudaDeviceSynchronize();
     if (e != cudaSuccess && rc == 0) { set_error("mgpu: device %u: %s", d, cudaGetErrorString(e)); rc = 1; }
   }
@@ -239,14 +261,14 @@ static int mgpu_colsplit(unsigned n_gpu, int32_t height, int32_t width, int32_t 
   int rc = 0;
   for (unsigned i = 0; i < n_gpu && rc == 0; ++i) {
     if (dim_gpu[i] <= 0) continue;  // trailing GPUs may get nothing
-    SBLAS_CUDA(cudaSetDevice(i));
+    SBLAS_CUDA(cudaSetDevice(device_of(i)));
     sblasPlan_t plan = plans ? plans[i] : nullptr;
     rc = sizeof(T) == 8
              ? sblas_spmm_csr_f64(nullptr, height, width, nnz, rp[i], ci[i], (const double*)val[i], dim_gpu[i], layout, (const double*)B[i], ldb[i], (double*)C[i], ldc[i], alpha, beta, plan, nullptr)
              : sblas_spmm_csr_f32(nullptr, height, width, nnz, rp[i], ci[i], (const float*)val[i], dim_gpu[i], layout, (const float*)B[i], ldb[i], (float*)C[i], ldc[i], alpha, beta, plan, nullptr);
   }
   for (unsigned d = 0; d < n_gpu; ++d) {
-    cudaSetDevice(d);
+    cudaSetDevice(device_of(d));
     cudaError_t e = cudaDeviceSynchronize();
     if (e != cudaSuccess && rc == 0) { set_error("mgpu: device %u: %s", d, cudaGetErrorString(e)); rc = 1; }
   }
@@ -258,6 +280,34 @@ static int mgpu_colsplit(unsigned n_gpu, int32_t height, int32_t width, int32_t 
 
 using namespace sblas;
 extern "C" {
+
+int sblas_device_of(int logical_gpu) { return device_of(logical_gpu); }
+
+// ---- CUDA-IPC shared replicas (one process per GPU: torchrun / torch.distributed) ------------
+int sblas_ipc_alloc(size_t bytes, void** ptr, unsigned char handle[64]) {
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+  SBLAS_CHECK(ptr && handle && bytes > 0, "ipc_alloc: bad arguments");
+  SBLAS_CUDA(cudaMalloc(ptr, bytes));
+  cudaIpcMemHandle_t h;
+  SBLAS_CUDA(cudaIpcGetMemHandle(&h, *ptr));
+  memcpy(handle, &h, 64);
+  return 0;
+}
+int sblas_ipc_open(const unsigned char handle[64], void** ptr) {
+  SBLAS_CHECK(ptr && handle, "ipc_open: bad arguments");
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle, 64);
+  SBLAS_CUDA(cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return 0;
+}
+int sblas_ipc_close(void* ptr) {
+  if (ptr) SBLAS_CUDA(cudaIpcCloseMemHandle(ptr));
+  return 0;
+}
+int sblas_ipc_free(void* ptr) {
+  if (ptr) SBLAS_CUDA(cudaFree(ptr));
+  return 0;
+}
 
 #define SBLAS_MGPU_SPMV(SFX, T)                                                                    \
   int sblas_mgpu_spmv_csr_v1_##SFX(unsigned n_gpu, int32_t height, int32_t width,                  \

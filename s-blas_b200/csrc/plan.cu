@@ -5,6 +5,7 @@
 
 namespace sblas {
 
+unsigned long long g_launches = 0;
 static thread_local char g_err[1024] = "";
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -126,6 +127,7 @@ using namespace sblas;
 extern "C" {
 
 int sblas_version(void) { return 100; }
+unsigned long long sblas_launch_count(void) { return g_launches; }
 const char* sblas_last_error(void) { return get_error(); }
 int sblas_device_count(void) {
   int n = 0;

@@ -364,6 +364,7 @@ static int spmm_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
       if (rc == 0) {
         kern<<<tt->n_tiles, kSpmmBlock, smem, st>>>(tt->d_tile_row, rp, ci, v, B, ldb, sink, cap,
                                                     o ? o->lanes : 0);
+        ++g_launches;
         cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) { set_error("spmm cm launch: %s", cudaGetErrorString(e)); rc = 3; }
       }

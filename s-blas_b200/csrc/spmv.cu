@@ -365,6 +365,7 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
         if ((rc = set_smem_once<T>((const void*)kern, smem)) == 0) {
           kern<<<tt->n_tiles, kSpmvBlock, smem, st>>>(tt->d_tile_row, rp, ci, v, x, sink, cap,
                                                       o ? o->lanes : 0);
+          ++g_launches;
           cudaError_t e = cudaGetLastError();
           if (e != cudaSuccess) { set_error("spmv tile launch: %s", cudaGetErrorString(e)); rc = 3; }
         }
@@ -405,6 +406,7 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
                                                     sink, carry_out, head_val, head_row, cap);
         spmv_split_fixup_kernel<T><<<(int)ceil_div(tt->n_tiles, 256), 256, 0, st>>>(
             rp, tile, tt->n_tiles, carry_out, head_val, head_row, sink);
+        g_launches += 2;
         cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) { set_error("spmv split launch: %s", cudaGetErrorString(e)); rc = 3; }
       }

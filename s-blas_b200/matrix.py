@@ -33,8 +33,14 @@ def _tdtype(npdt):
     return torch.float64 if np.dtype(npdt) == np.float64 else torch.float32
 
 
+def physical(i):
+    """CUDA device ordinal of logical GPU i (SBLAS_DEVICE_MAP, see sblas_device_of)."""
+    from ._lib import lib
+    return int(lib().sblas_device_of(int(i)))
+
+
 def _dev(i):
-    return _torch().device("cuda", i)
+    return _torch().device("cuda", physical(i))
 
 
 def _to_dev(a, i):
@@ -77,7 +83,7 @@ class CsrSparseMatrix:
                 self.csrRowPtr_gpu.append(_to_dev(self.csrRowPtr, i))
                 self.csrColIdx_gpu.append(_to_dev(self.csrColIdx, i))
                 self.csrVal_gpu.append(_to_dev(self.csrVal, i))
-                with torch.cuda.device(i):
+                with torch.cuda.device(physical(i)):
                     self.plans.append(K.Plan(self.csrRowPtr_gpu[i], self.nnz))
         else:
             p = K.csr_partition_nnz(self.csrRowPtr, n_gpu)
@@ -90,7 +96,7 @@ class CsrSparseMatrix:
                 self.csrRowPtr_gpu.append(_to_dev(p["rowptr"][i], i))
                 self.csrColIdx_gpu.append(_to_dev(self.csrColIdx[lo:lo + n_i], i))
                 self.csrVal_gpu.append(_to_dev(self.csrVal[lo:lo + n_i], i))
-                with torch.cuda.device(i):
+                with torch.cuda.device(physical(i)):
                     self.plans.append(K.Plan(self.csrRowPtr_gpu[i], n_i) if n_i > 0 and
                                       len(p["rowptr"][i]) else None)
                 if not quiet:                                               # matrix.h:388
@@ -128,10 +134,10 @@ class DenseVector:
     def plusDenseVectorGPU(self, dv, alpha, beta):                          # matrix.h:714-726
         torch = _torch()
         for i in range(self.n_gpu):
-            with torch.cuda.device(i):
+            with torch.cuda.device(physical(i)):
                 K.axpby(self.val_gpu[i], dv.val_gpu[i], alpha, beta)
         for i in range(self.n_gpu):
-            torch.cuda.synchronize(i)
+            torch.cuda.synchronize(physical(i))
 
     def get_vec_length(self):
         return self.length
@@ -189,7 +195,7 @@ class DenseMatrix:
             if self.order == col_major and self.dev_layout == ROW_MAJOR:
                 ld = (dims[i] + vec - 1) // vec * vec
                 dst = torch.zeros(second * ld, dtype=stage.dtype, device=_dev(i))
-                with torch.cuda.device(i):
+                with torch.cuda.device(physical(i)):
                     K.transpose(stage, second, dims[i], second, dst, ld)
                     torch.cuda.synchronize()
                 self.val_gpu.append(dst)
@@ -211,7 +217,7 @@ class DenseMatrix:
         src = self.val_gpu[i_gpu]
         if self.order == col_major and self.dev_layout == ROW_MAJOR:
             tmp = torch.empty(dim * second, dtype=src.dtype, device=src.device)
-            with torch.cuda.device(i_gpu):
+            with torch.cuda.device(physical(i_gpu)):
                 K.transpose(src, self.ld_gpu[i_gpu], second, dim, tmp, second)
                 torch.cuda.synchronize()
             src = tmp
@@ -220,7 +226,7 @@ class DenseMatrix:
     def plusDenseMatrixGPU(self, dm, alpha, beta):                          # matrix.h:613-625
         torch = _torch()
         for i in range(self.n_gpu):
-            with torch.cuda.device(i):
+            with torch.cuda.device(physical(i)):
                 K.axpby(self.val_gpu[i], dm.val_gpu[i], alpha, beta)
         for i in range(self.n_gpu):
-            torch.cuda.synchronize(i)
+            torch.cuda.synchronize(physical(i))

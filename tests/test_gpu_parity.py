@@ -1,0 +1,300 @@
+"""Parity of the CUDA path (through the C ABI) against the CPU oracle / the reference goldens.
+
+Bars (north star): bit-exact for integer work and for the sequential kernel paths; otherwise
+per-row error <= 1e-12 (fp64) / 1e-5 (fp32) relative to (|A||x|)_i."""
+import numpy as np
+import pytest
+
+import synth_ref as SR
+
+pytestmark = pytest.mark.gpu
+
+TOL = {np.dtype(np.float64): 1e-12, np.dtype(np.float32): 1e-5}
+
+
+def _t(dev, a):
+    import torch
+    return torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+
+
+def _rand_csr(rng, h, w, avg, empty=0.2, long_row=None, dtype=np.float64, sort=True):
+    lens = rng.poisson(avg, h).astype(np.int64)
+    lens[rng.random(h) < empty] = 0
+    if long_row:
+        lens[long_row[0]] = long_row[1]
+    lens = np.minimum(lens, w)
+    rp = np.zeros(h + 1, np.int32)
+    rp[1:] = np.cumsum(lens)
+    ci = np.zeros(rp[-1], np.int32)
+    for i in range(h):
+        c = rng.choice(w, lens[i], replace=False)
+        ci[rp[i]:rp[i + 1]] = np.sort(c) if sort else c
+    v = (rng.random(rp[-1]) * 2 - 1).astype(dtype)
+    return rp, ci, v
+
+
+def _row_bound(oracle, rp, ci, v, x, alpha, beta, y0):
+    """|alpha|*(|A||x|)_i + |beta*y0_i|: the scale the tolerance is relative to."""
+    return abs(alpha) * oracle.absrow_spmv(rp, ci, v, x) + np.abs(beta * y0.astype(np.float64)) + 1e-300
+
+
+def _check(got, ref, bound, dtype, exact=False):
+    if exact:
+        assert np.array_equal(got, ref), "not bit-identical: max |d| = %g" % np.abs(got - ref).max()
+    else:
+        err = np.abs(got.astype(np.float64) - ref.astype(np.float64)) / bound
+        assert err.max() <= TOL[np.dtype(dtype)], "max rel row error %g" % err.max()
+
+
+# ------------------------------------------------------------------------------------ SpMV ----
+MATS = {
+    "short": dict(h=3000, w=3000, avg=4, empty=0.3),
+    "mid": dict(h=1500, w=1500, avg=40, empty=0.05),
+    "long": dict(h=600, w=20000, avg=300, empty=0.0),
+    "skew": dict(h=800, w=30000, avg=5, empty=0.4, long_row=(333, 25000)),
+    "empty_tail": dict(h=2000, w=500, avg=0.2, empty=0.8),
+    "tiny": dict(h=1, w=7, avg=3, empty=0.0),
+}
+
+
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+@pytest.mark.parametrize("mat", list(MATS))
+@pytest.mark.parametrize("variant", ["auto", "tile", "vector", "split", "noplan"])
+def test_spmv_vs_oracle(sblas, dev, oracle, dtype, mat, variant):
+    import torch
+    K = sblas.kernels
+    rng = np.random.default_rng(hash((mat, variant)) % 1000)
+    kw = MATS[mat]
+    rp, ci, v = _rand_csr(rng, kw["h"], kw["w"], kw["avg"], kw["empty"], kw.get("long_row"), dtype)
+    h, w = kw["h"], kw["w"]
+    x = rng.random(w).astype(dtype)
+    y0 = rng.random(h).astype(dtype)
+    alpha, beta = dtype(1.25), dtype(-0.75)
+    ref = oracle.spmv(rp, ci, v, x, y0.copy(), alpha, beta)
+    drp, dci, dv, dx, dy = (_t(dev, a) for a in (rp, ci, v, x, y0))
+    plan = None if variant == "noplan" else K.Plan(drp, len(ci))
+    var = dict(auto=0, noplan=0, tile=sblas.SPMV_TILE, vector=sblas.SPMV_VECTOR, split=sblas.SPMV_SPLIT)[variant]
+    opts = sblas.make_opts(variant=var, tile=512 if variant in ("tile", "split") else 0)
+    K.spmv(drp, dci, dv, dx, dy, alpha, beta, plan=plan, opts=opts)
+    torch.cuda.synchronize()
+    bound = _row_bound(oracle, rp, ci, v, x, alpha, beta, y0)
+    _check(dy.cpu().numpy(), ref, bound, dtype)
+
+
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_spmv_short_rows_bit_identical(sblas, dev, oracle, dtype):
+    """Rows reduced by one lane in CSR order with rounded mul/add == the reference CPU loop."""
+    import torch
+    K = sblas.kernels
+    rp, ci, v = SR.laplace2d(97, 53, dtype)
+    n = 97 * 53
+    x = SR.fill_uniform(n, 211, 7, 0, 1, dtype)
+    for alpha, beta in ((1.0, 1.0), (3.0, 4.0), (0.5, 0.0)):
+        ref = oracle.spmv(rp, ci, v, x, np.ones(n, dtype), dtype(alpha), dtype(beta))
+        drp, dci, dv, dx, dy = (_t(dev, a) for a in (rp, ci, v, x, np.ones(n, dtype)))
+        K.spmv(drp, dci, dv, dx, dy, alpha, beta, plan=K.Plan(drp, len(ci)))
+        torch.cuda.synchronize()
+        assert np.array_equal(dy.cpu().numpy(), ref)
+        dy2 = _t(dev, np.ones(n, dtype))
+        K.spmv(drp, dci, dv, dx, dy2, alpha, beta, plan=K.Plan(drp, len(ci)),
+               opts=sblas.make_opts(variant=sblas.SPMV_TILE, lanes=1, tile=777))
+        assert np.array_equal(dy2.cpu().numpy(), ref)
+
+
+def test_spmv_golden_ash85(sblas, dev, golden):
+    """BASELINE config 1: ash85, x = y = 1, alpha = beta = 1 -> y = 1 + rowlen, sum 608."""
+    import torch
+    K = sblas.kernels
+    h, w, rp, ci, v = K.read_mtx(golden["ash85_path"])
+    drp, dci, dv = (_t(dev, a) for a in (rp, ci, v))
+    dy = torch.ones(h, dtype=torch.float64, device=dev)
+    K.spmv(drp, dci, dv, torch.ones(w, dtype=torch.float64, device=dev), dy, 1.0, 1.0,
+           plan=K.Plan(drp, len(ci)))
+    y = dy.cpu().numpy()
+    assert np.array_equal(y, golden["ash_spmv_ones"]) and y.sum() == 608.0
+    dy = torch.ones(h, dtype=torch.float64, device=dev)
+    K.spmv(drp, dci, dv, _t(dev, golden["ash_x_rand"]), dy, 3.0, 4.0, plan=K.Plan(drp, len(ci)))
+    assert np.array_equal(dy.cpu().numpy(), golden["ash_spmv_rand_a3b4"])
+
+
+@pytest.mark.parametrize("name", ["rnd_short", "rnd_mid"])
+@pytest.mark.parametrize("sfx", ["f64", "f32"])
+def test_spmv_reference_goldens(sblas, dev, oracle, golden, name, sfx):
+    K = sblas.kernels
+    key = "%s_%s" % (name, sfx)
+    m = golden["meta"][key]
+    dt = np.float64 if sfx == "f64" else np.float32
+    rp, ci, v, x, y0 = (golden[key + s] for s in ("_rp", "_ci", "_v", "_x", "_y0"))
+    drp, dci, dv, dx, dy = (_t(dev, a) for a in (rp, ci, v, x, y0))
+    K.spmv(drp, dci, dv, dx, dy, m["alpha"], m["beta"], plan=K.Plan(drp, len(ci)))
+    bound = _row_bound(oracle, rp, ci, v, x, m["alpha"], m["beta"], y0)
+    _check(dy.cpu().numpy(), golden[key + "_spmv"], bound, dt)
+
+
+def test_spmv_partials_and_replicas(sblas, dev, oracle):
+    """HEAD/TAIL partial rows go to the carry buffer, everything else to y and every replica."""
+    import torch
+    K = sblas.kernels
+    rng = np.random.default_rng(5)
+    rp, ci, v = _rand_csr(rng, 500, 500, 9, 0.1)
+    x, y0 = rng.random(500), rng.random(500)
+    ref = oracle.spmv(rp, ci, v, x, y0.copy(), 2.0, 0.5)
+    raw = oracle.spmv(rp, ci, v, x, np.zeros(500), 1.0, 0.0)
+    for var in (sblas.SPMV_TILE, sblas.SPMV_VECTOR, sblas.SPMV_SPLIT):
+        drp, dci, dv, dx, dy = (_t(dev, a) for a in (rp, ci, v, x, y0))
+        rep = torch.full((500,), -7.0, dtype=torch.float64, device=dev)
+        carry = torch.zeros(8, dtype=torch.float64, device=dev)
+        o = sblas.make_opts(variant=var, flags=sblas.FLAG_HEAD_PARTIAL | sblas.FLAG_TAIL_PARTIAL,
+                            replicas=[rep.data_ptr()], carry=carry.data_ptr(), tile=256)
+        K.spmv(drp, dci, dv, dx, dy, 2.0, 0.5, plan=K.Plan(drp, len(ci)), opts=o)
+        y, r, c = dy.cpu().numpy(), rep.cpu().numpy(), carry.cpu().numpy()
+        bound = _row_bound(oracle, rp, ci, v, x, 2.0, 0.5, y0)
+        _check(y[1:-1], ref[1:-1], bound[1:-1], np.float64)
+        assert np.array_equal(r[1:-1], y[1:-1])
+        assert y[0] == y0[0] and y[-1] == y0[-1] and r[0] == -7.0 and r[-1] == -7.0
+        assert abs(c[0] - raw[0]) <= 1e-12 * bound[0] and abs(c[1] - raw[-1]) <= 1e-12 * bound[-1]
+
+
+# ------------------------------------------------------------------------------------ SpMM ----
+def _spmm_ref(oracle, rp, ci, v, k, Bc, C0c, alpha, beta):
+    return oracle.spmm(rp, ci, v, k, Bc, C0c.copy(), alpha, beta)
+
+
+def _to_rm(a_cm, rows, k, ld):
+    out = np.zeros((rows, ld), a_cm.dtype)
+    out[:, :k] = a_cm.reshape(k, rows).T
+    return out.reshape(-1)
+
+
+def _from_rm(a_rm, rows, k, ld):
+    return np.ascontiguousarray(a_rm.reshape(rows, ld)[:, :k].T).reshape(-1)
+
+
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+@pytest.mark.parametrize("k", [1, 3, 8, 12, 32, 64, 100, 256, 700])
+@pytest.mark.parametrize("mat", ["short", "mid", "skew"])
+def test_spmm_rowmajor_bit_identical(sblas, dev, oracle, dtype, k, mat):
+    """Every (row, column) sum is accumulated by one lane in CSR order with rounded mul/add:
+    bit-identical to sblas_spmm_csr_cpu (spmm.h:55-68)."""
+    import torch
+    K = sblas.kernels
+    kw = dict(MATS[mat])
+    if mat == "skew":
+        kw.update(h=200, w=3000, long_row=(77, 2500))
+    else:
+        kw.update(h=min(kw["h"], 400), w=min(kw["w"], 400))
+    rng = np.random.default_rng(k)
+    rp, ci, v = _rand_csr(rng, kw["h"], kw["w"], kw["avg"], kw["empty"], kw.get("long_row"), dtype,
+                          sort=False)
+    h, w = kw["h"], kw["w"]
+    Bc, C0c = rng.random(w * k).astype(dtype), rng.random(h * k).astype(dtype)
+    alpha, beta = dtype(1.5), dtype(-0.5)
+    ref = _spmm_ref(oracle, rp, ci, v, k, Bc, C0c, alpha, beta)
+    vec = 16 // np.dtype(dtype).itemsize
+    for ld in ((k + vec - 1) // vec * vec, k + 1 if k % vec == 0 else k):   # vector path, scalar path
+        dB, dC = _t(dev, _to_rm(Bc, w, k, ld)), _t(dev, _to_rm(C0c, h, k, ld))
+        drp, dci, dv = (_t(dev, a) for a in (rp, ci, v))
+        K.spmm(drp, dci, dv, k, sblas.ROW_MAJOR, dB, ld, dC, ld, alpha, beta, w, plan=K.Plan(drp, len(ci)))
+        torch.cuda.synchronize()
+        got = _from_rm(dC.cpu().numpy(), h, k, ld)
+        assert np.array_equal(got, ref), "k=%d ld=%d max|d|=%g" % (k, ld, np.abs(got - ref).max())
+
+
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+@pytest.mark.parametrize("k", [1, 5, 64])
+@pytest.mark.parametrize("mat", ["short", "mid"])
+def test_spmm_colmajor_vs_oracle(sblas, dev, oracle, dtype, k, mat):
+    import torch
+    K = sblas.kernels
+    kw = MATS[mat]
+    h = w = 500
+    rng = np.random.default_rng(k + 17)
+    rp, ci, v = _rand_csr(rng, h, w, kw["avg"], kw["empty"], None, dtype)
+    Bc, C0c = rng.random(w * k).astype(dtype), rng.random(h * k).astype(dtype)
+    alpha, beta = dtype(0.75), dtype(2.0)
+    ref = _spmm_ref(oracle, rp, ci, v, k, Bc, C0c, alpha, beta)
+    drp, dci, dv, dB, dC = (_t(dev, a) for a in (rp, ci, v, Bc, C0c))
+    K.spmm(drp, dci, dv, k, sblas.COL_MAJOR, dB, w, dC, h, alpha, beta, w, plan=K.Plan(drp, len(ci)))
+    torch.cuda.synchronize()
+    got = dC.cpu().numpy()
+    # bound per (row, column): reuse the SpMV bound column by column
+    for n in range(k):
+        b = _row_bound(oracle, rp, ci, v, Bc[n * w:(n + 1) * w], alpha, beta, C0c[n * h:(n + 1) * h])
+        _check(got[n * h:(n + 1) * h], ref[n * h:(n + 1) * h], b, dtype)
+
+
+def test_spmm_fma_flag_within_tolerance(sblas, dev, oracle):
+    import torch
+    K = sblas.kernels
+    rng = np.random.default_rng(2)
+    h = w = 300
+    k = 64
+    rp, ci, v = _rand_csr(rng, h, w, 20, 0.1)
+    Bc, C0c = rng.random(w * k), rng.random(h * k)
+    ref = _spmm_ref(oracle, rp, ci, v, k, Bc, C0c, 1.0, 1.0)
+    dB, dC = _t(dev, _to_rm(Bc, w, k, k)), _t(dev, _to_rm(C0c, h, k, k))
+    drp, dci, dv = (_t(dev, a) for a in (rp, ci, v))
+    K.spmm(drp, dci, dv, k, sblas.ROW_MAJOR, dB, k, dC, k, 1.0, 1.0, w, plan=K.Plan(drp, len(ci)),
+           opts=sblas.make_opts(flags=sblas.FLAG_FMA))
+    got = _from_rm(dC.cpu().numpy(), h, k, k)
+    for n in range(0, k, 9):
+        b = _row_bound(oracle, rp, ci, v, Bc[n * w:(n + 1) * w], 1.0, 1.0, C0c[n * h:(n + 1) * h])
+        _check(got[n * h:(n + 1) * h], ref[n * h:(n + 1) * h], b, np.float64)
+
+
+@pytest.mark.parametrize("k", [64, 256, 9])
+def test_spmm_golden_ash85(sblas, dev, golden, oracle, k):
+    """BASELINE config 1 (k=64, alpha=beta=1) and unit_test.cu:183 (k=256, alpha=3, beta=4)."""
+    K = sblas.kernels
+    m = golden["meta"]["ash85"]["spmm_k%d" % k]
+    h, w, rp, ci, v = K.read_mtx(golden["ash85_path"])
+    Bc = oracle.rand_fill(w * k)            # DenseMatrix(w, k, col_major) ctor, seed 211
+    ld = (k + 1) // 2 * 2
+    dB, dC = _t(dev, _to_rm(Bc, w, k, ld)), _t(dev, _to_rm(np.ones(h * k), h, k, ld))
+    drp, dci, dv = (_t(dev, a) for a in (rp, ci, v))
+    K.spmm(drp, dci, dv, k, sblas.ROW_MAJOR, dB, ld, dC, ld, m["alpha"], m["beta"], w,
+           plan=K.Plan(drp, len(ci)))
+    got = _from_rm(dC.cpu().numpy(), h, k, ld)
+    assert np.array_equal(got, golden["ash_spmm_k%d" % k])
+    if k == 64:
+        assert got[0] == 3.6699169691046314
+
+
+# ---------------------------------------------------------------------------- utility kernels ----
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_axpby_scal_transpose(sblas, dev, oracle, dtype):
+    import torch
+    K = sblas.kernels
+    rng = np.random.default_rng(1)
+    for n in (1, 7, 1000, 100003):
+        a, b = rng.random(n).astype(dtype), rng.random(n).astype(dtype)
+        ref = oracle.axpby(a.copy(), b, dtype(3.0), dtype(4.0))
+        da = _t(dev, a)
+        K.axpby(da, _t(dev, b), 3.0, 4.0)
+        assert np.array_equal(da.cpu().numpy(), ref)                      # kernel.h:34 order
+        db = _t(dev, a)
+        K.scal_add(db, 0.5, 2.0)
+        assert np.array_equal(db.cpu().numpy(), a * dtype(2.0) + dtype(0.5))
+    for (r, c, ld_in, ld_out) in ((5, 3, 3, 5), (100, 64, 64, 100), (33, 65, 70, 40), (1000, 7, 7, 1003)):
+        src = rng.random(r * ld_in).astype(dtype)
+        dst = torch.zeros(c * ld_out, dtype=_t(dev, src).dtype, device=dev)
+        K.transpose(_t(dev, src), ld_in, r, c, dst, ld_out)
+        got = dst.cpu().numpy().reshape(c, ld_out)[:, :r]
+        assert np.array_equal(got, src.reshape(r, ld_in)[:, :c].T)
+
+
+# ------------------------------------------------------------------------------- generators ----
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_synth_generators_match_numpy(sblas, dev, dtype):
+    import torch
+    S = sblas.synth
+    td = torch.float64 if dtype == np.float64 else torch.float32
+    t = S.fill_uniform(torch.empty(1000, dtype=td, device=dev), 211, 5, -1.0, 1.0)
+    assert np.array_equal(t.cpu().numpy(), SR.fill_uniform(1000, 211, 5, -1.0, 1.0, dtype))
+    for got, ref in ((S.laplace2d(37, 29, td, dev), SR.laplace2d(37, 29, dtype)),
+                     (S.uniform(300, 5000, 32, td, dev), SR.uniform(300, 5000, 32, 211, dtype)),
+                     (S.banded(500, 64, td, dev), SR.banded(500, 64, 211, dtype)),
+                     (S.rmat(10, 8, td, dev), SR.rmat(10, 8, 211, dtype))):
+        for g, r in zip(got[2:], ref):
+            assert np.array_equal(g.cpu().numpy(), r)
+    assert S.laplace2d(2048, 2048, td, dev)[4].numel() == 20963328
