@@ -29,14 +29,14 @@ template <typename T>
 struct RowSink {
   T* y;
   OutSpec<T> out;
-  T* carry;       // [2] head / tail partial sums
+  T* carry;       // head partial sum at [0], tail partial sum at [4] (= kpad of k = 1, sblas_b200.h)
   int32_t rows;   // local row count
   int32_t flags;  // HEAD_PARTIAL | TAIL_PARTIAL
   T alpha, beta;
 
   __device__ __forceinline__ void put(int32_t r, T sum) const {
     if ((flags & SBLAS_FLAG_HEAD_PARTIAL) && r == 0) { carry[0] = sum; return; }
-    if ((flags & SBLAS_FLAG_TAIL_PARTIAL) && r == rows - 1) { carry[1] = sum; return; }
+    if ((flags & SBLAS_FLAG_TAIL_PARTIAL) && r == rows - 1) { carry[4] = sum; return; }
     T res = axpby_rn(alpha, sum, beta, y[r]);
     y[r] = res;
     for (int d = 0; d < out.n; ++d) out.ptr[d][r] = res;
