@@ -254,6 +254,7 @@ def run_ours(args, wl_key):
         cfg_extra["panel_rows"] = [int(rb[i + 1] - rb[i]) for i in range(world)]
 
     flush = torch.empty(2 * L2_BYTES // 4, dtype=torch.int32, device=dev)
+    flush_rd = torch.ones_like(flush)
 
     def barrier():
         torch.cuda.synchronize()
@@ -267,8 +268,9 @@ def run_ours(args, wl_key):
         ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
               for _ in range(steps)]
         for a, b in ev:
-            flush.zero_()
-            a.record()
+            flush.zero_()        # write 252 MiB: evicts every line of the previous step
+            flush_rd.sum()       # then read 252 MiB: L2 is left full of CLEAN lines, so the step is
+            a.record()           # not billed for the write-back of the flush buffer's dirty lines
             fn()
             b.record()
         torch.cuda.synchronize()
@@ -355,7 +357,7 @@ def run_ours(args, wl_key):
             "config": dict({"workload": wl_key + ": " + wl["name"], "rows": rows, "cols": cols,
                             "nnz": nnz, "k": k, "alpha": 1.0, "beta": 1.0, "index": "int32",
                             "timing": "CUDA events per step on the launching stream; L2 flushed "
-                                      "(%d MiB memset) between steps; inputs %s L2" % (
+                                      "(%d MiB memset + clean read sweep of a second buffer) between steps; inputs %s L2" % (
                                           2 * L2_BYTES >> 20, "larger than" if abytes > L2_BYTES else "smaller than"),
                             "ms_per_step_back_to_back_no_flush": ms_b2b,
                             "wall_ms_timed_region": wall_ms,

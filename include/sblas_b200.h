@@ -50,6 +50,8 @@ enum {
   SBLAS_SPMV_TILE = 1,    /* nnz-balanced row-aligned merge-path tiles, smem-staged products */
   SBLAS_SPMV_VECTOR = 2,  /* sub-warp (2..32 lanes) per row, no plan needed */
   SBLAS_SPMV_SPLIT = 3,   /* merge-path tiles that split long rows, carry fix-up (skewed inputs) */
+  SBLAS_SPMV_PIPE = 4,    /* TILE's tiles walked by persistent CTAs; col_idx/val/rowptr/y of the next
+                             tiles staged by TMA bulk copies + LDGSTS behind mbarriers (AUTO's choice) */
   SBLAS_SPMM_ROWMAJOR = 1, /* internal row-major B/C: one lane group per A row, 128-bit B gathers */
   SBLAS_SPMM_COLMAJOR = 2  /* native col-major B/C (the reference's host layout), no transposes */
 };
@@ -70,7 +72,7 @@ typedef struct sblasOpts {
   int32_t tile;      /* tile size in merge items, 0 = auto */
   int32_t lanes;     /* lanes per row for the vector variants, 0 = auto */
   int32_t n_replica; /* extra copies of the output to store (peer GPUs' replicas), <= 15 */
-  int32_t reserved;
+  int32_t stages;    /* pipeline depth of SBLAS_SPMV_PIPE (2..4), 0 = auto */
   void* replica[SBLAS_MAX_GPU - 1]; /* same logical base pointer as y / C on each peer */
   void* carry;       /* device buffer of 2*((k+3)&~3) DataType: HEAD sums at [0,k), TAIL sums at
                         [(k+3)&~3, ...) (k = 1 for SpMV) */
@@ -166,6 +168,60 @@ SBLAS_API int sblas_transpose_f64(void* stream, const double* d_in, int64_t in_l
                                   int64_t n_minor, double* d_out, int64_t out_ld);
 SBLAS_API int sblas_transpose_f32(void* stream, const float* d_in, int64_t in_ld, int64_t n_major,
                                   int64_t n_minor, float* d_out, int64_t out_ld);
+
+/* ---- memory plumbing used by the C++ drop-in headers -------------------------------------
+ * Replaces the allocation macros of utility.h:86-127 (SAFE_ALOC_HOST = cudaMallocHost,
+ * SAFE_ALOC_GPU = cudaMalloc, SAFE_FREE_*) and the cudaMemcpy calls of matrix.h:341-387,
+ * :541-570, :595-612, :688-713.  `gpu` is a LOGICAL GPU ordinal (sblas_device_of).  With these
+ * the headers need no CUDA toolkit on the include path.
+ * sblas_host_alloc returns pinned memory; with no CUDA driver at all it returns ordinary
+ * aligned memory so that the host-side integer layer can still be exercised (no kernel can
+ * run in that case anyway). */
+SBLAS_API int sblas_host_alloc(size_t bytes, void** h_ptr);
+SBLAS_API int sblas_host_free(void* h_ptr);
+SBLAS_API int sblas_dev_alloc(int gpu, size_t bytes, void** d_ptr);
+SBLAS_API int sblas_dev_free(int gpu, void* d_ptr);
+SBLAS_API int sblas_copy_h2d(int gpu, void* d_dst, const void* h_src, size_t bytes);
+SBLAS_API int sblas_copy_d2h(int gpu, void* h_dst, const void* d_src, size_t bytes);
+SBLAS_API int sblas_copy_d2d(int gpu, void* d_dst, const void* d_src, size_t bytes);
+SBLAS_API int sblas_dev_memset(int gpu, void* d_ptr, int value, size_t bytes);
+SBLAS_API int sblas_dev_sync(int gpu);
+/* sblas_plan_create_i32 and sblas_axpby_* (kernel.h:28-37 as launched by
+ * plusDenseVectorGPU / plusDenseMatrixGPU, matrix.h:613-625, :714-726) on a logical GPU's
+ * default stream; alpha/beta are narrowed to float when is_f64 == 0. */
+SBLAS_API int sblas_plan_create_on(int gpu, int32_t rows, int64_t nnz, const int32_t* d_rowptr,
+                                   sblasPlan_t* plan);
+SBLAS_API int sblas_axpby_on(int gpu, int is_f64, void* d_v0, const void* d_v1, double alpha,
+                             double beta, int64_t n);
+SBLAS_API int sblas_scal_add_on(int gpu, int is_f64, void* d_v, double val, double beta, int64_t n);
+/* DenseMatrix::sync2gpu / sync2cpu for one GPU's slice (matrix.h:541-570, :595-612).  h is the
+ * host slice: `dim` leading-dimension lines of `second` contiguous elements each (for the
+ * col_major operands of SpMM: dim columns of `second` rows).  dev_layout SBLAS_COL_MAJOR keeps
+ * that layout on the device (ld = second), SBLAS_ROW_MAJOR stores the transposed slice
+ * [second x ld] with ld = dim rounded up to 16 bytes (the layout the ROWMAJOR kernel wants).
+ * The upload allocates *d_out (release with sblas_dev_free). */
+SBLAS_API int sblas_dense_upload_f64(int gpu, const double* h, int64_t second, int64_t dim,
+                                     int32_t dev_layout, double** d_out, int64_t* ld_out);
+SBLAS_API int sblas_dense_upload_f32(int gpu, const float* h, int64_t second, int64_t dim,
+                                     int32_t dev_layout, float** d_out, int64_t* ld_out);
+SBLAS_API int sblas_dense_download_f64(int gpu, const double* d, int64_t ld, int64_t second,
+                                       int64_t dim, int32_t dev_layout, double* h);
+SBLAS_API int sblas_dense_download_f32(int gpu, const float* d, int64_t ld, int64_t second,
+                                       int64_t dim, int32_t dev_layout, float* h);
+/* Managed memory of the matrix_um.h variants: cudaMallocManaged (matrix_um.h:60-75),
+ * cudaMemAdvise / cudaMemPrefetchAsync (matrix_um.h:529-614).  gpu = -1 means the CPU. */
+enum {
+  SBLAS_ADVISE_SET_READ_MOSTLY = 1,
+  SBLAS_ADVISE_UNSET_READ_MOSTLY = 2,
+  SBLAS_ADVISE_SET_PREFERRED_LOCATION = 3,
+  SBLAS_ADVISE_UNSET_PREFERRED_LOCATION = 4,
+  SBLAS_ADVISE_SET_ACCESSED_BY = 5,
+  SBLAS_ADVISE_UNSET_ACCESSED_BY = 6
+};
+SBLAS_API int sblas_managed_alloc(size_t bytes, void** ptr);
+SBLAS_API int sblas_managed_free(void* ptr);
+SBLAS_API int sblas_mem_advise(void* ptr, size_t bytes, int advice, int gpu);
+SBLAS_API int sblas_mem_prefetch(void* ptr, size_t bytes, int gpu);
 
 /* ---- multi-GPU ops, one process driving GPUs 0..n_gpu-1 (the reference's execution model:
  *      spmv.h:52-55, spmm.h:101-104; streams/events/peer access live in a cached context) ---- */

@@ -10,7 +10,7 @@ LIB_PATH = os.path.join(HERE, "lib", "libsblas_b200.so")
 
 MAX_GPU = 16
 # enums of include/sblas_b200.h
-VARIANT_AUTO, SPMV_TILE, SPMV_VECTOR, SPMV_SPLIT = 0, 1, 2, 3
+VARIANT_AUTO, SPMV_TILE, SPMV_VECTOR, SPMV_SPLIT, SPMV_PIPE = 0, 1, 2, 3, 4
 SPMM_ROWMAJOR, SPMM_COLMAJOR = 1, 2
 FLAG_FMA, FLAG_HEAD_PARTIAL, FLAG_TAIL_PARTIAL, FLAG_NO_L1 = 1, 2, 4, 8
 ROW_MAJOR, COL_MAJOR = 0, 1
@@ -22,7 +22,7 @@ class SblasError(RuntimeError):
 
 class Opts(C.Structure):
     _fields_ = [("variant", C.c_int32), ("flags", C.c_int32), ("tile", C.c_int32),
-                ("lanes", C.c_int32), ("n_replica", C.c_int32), ("reserved", C.c_int32),
+                ("lanes", C.c_int32), ("n_replica", C.c_int32), ("stages", C.c_int32),
                 ("replica", C.c_void_p * (MAX_GPU - 1)), ("carry", C.c_void_p)]
 
 
@@ -57,9 +57,9 @@ def check(rc, what=""):
                                                  lib().sblas_last_error().decode()))
 
 
-def make_opts(variant=0, flags=0, tile=0, lanes=0, replicas=(), carry=None):
+def make_opts(variant=0, flags=0, tile=0, lanes=0, replicas=(), carry=None, stages=0):
     o = Opts()
-    o.variant, o.flags, o.tile, o.lanes = variant, flags, tile, lanes
+    o.variant, o.flags, o.tile, o.lanes, o.stages = variant, flags, tile, lanes, stages
     o.n_replica = len(replicas)
     for i, p in enumerate(replicas):
         o.replica[i] = p

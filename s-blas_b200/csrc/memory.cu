@@ -1,0 +1,242 @@
+// memory.cu — memory plumbing behind the C++ drop-in headers (include/matrix.h, matrix_um.h).
+//
+// The reference's data model allocates pinned host arrays and per-GPU device arrays with the
+// macros of utility.h:86-127 and moves them with plain cudaMemcpy (matrix.h:341-387, :541-570,
+// :595-612, :688-713); the managed-memory variant uses cudaMallocManaged + cudaMemAdvise +
+// cudaMemPrefetchAsync (matrix_um.h:529-614).  The drop-in headers make the same moves
+// through these entry points, so they compile with a plain C++ compiler (no CUDA toolkit on
+// the include path) and every CUDA call of the product lives inside libsblas_b200.so.
+// `gpu` is always a LOGICAL GPU ordinal (sblas_device_of).
+#include <stdlib.h>
+
+#include "common.cuh"
+
+namespace sblas {
+
+static int g_has_device = -1;  // decided once: pinned host memory needs a driver
+static bool has_device() {
+  if (g_has_device < 0) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); n = 0; }
+    g_has_device = n > 0 ? 1 : 0;
+  }
+  return g_has_device == 1;
+}
+
+struct DeviceScope {  // cudaSetDevice(device_of(gpu)) for the lifetime of the object
+  int prev = -1;
+  bool ok = true;
+  explicit DeviceScope(int gpu) {
+    if (cudaGetDevice(&prev) != cudaSuccess) { ok = false; return; }
+    if (cudaSetDevice(sblas_device_of(gpu)) != cudaSuccess) ok = false;
+  }
+  ~DeviceScope() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+#define SBLAS_ON_GPU(gpu)                                                                  \
+  DeviceScope scope__(gpu);                                                                \
+  if (!scope__.ok) {                                                                       \
+    set_error("cannot select logical GPU %d (device %d): %s", gpu, sblas_device_of(gpu),   \
+              cudaGetErrorString(cudaGetLastError()));                                     \
+    return 1;                                                                              \
+  }
+
+template <typename T>
+static int dense_upload(int gpu, const T* h_src, int64_t second, int64_t dim, int32_t layout,
+                        T** d_out, int64_t* ld_out) {
+  SBLAS_CHECK(d_out && ld_out && second >= 0 && dim >= 0, "dense_upload: bad arguments");
+  *d_out = nullptr;
+  *ld_out = layout == SBLAS_ROW_MAJOR ? 1 : second;
+  if (second == 0 || dim == 0) return 0;
+  SBLAS_CHECK(h_src, "dense_upload: null source");
+  SBLAS_ON_GPU(gpu);
+  const size_t bytes = sizeof(T) * (size_t)second * (size_t)dim;
+  T* stage = nullptr;
+  SBLAS_CUDA(cudaMalloc(&stage, bytes));
+  SBLAS_CUDA(cudaMemcpy(stage, h_src, bytes, cudaMemcpyHostToDevice));
+  if (layout == SBLAS_COL_MAJOR) {  // the reference's device layout: slice as is
+    *d_out = stage;
+    *ld_out = second;
+    return 0;
+  }
+  // internal layout: row-major [second x ld], ld = dim rounded up to a 16-byte multiple
+  constexpr int64_t VF = 16 / sizeof(T);
+  const int64_t ld = (dim + VF - 1) / VF * VF;
+  T* dst = nullptr;
+  SBLAS_CUDA(cudaMalloc(&dst, sizeof(T) * (size_t)second * (size_t)ld));
+  if (ld != dim) SBLAS_CUDA(cudaMemset(dst, 0, sizeof(T) * (size_t)second * (size_t)ld));
+  int rc = sizeof(T) == 8
+               ? sblas_transpose_f64(nullptr, (const double*)stage, second, dim, second, (double*)dst, ld)
+               : sblas_transpose_f32(nullptr, (const float*)stage, second, dim, second, (float*)dst, ld);
+  if (rc) return rc;
+  SBLAS_CUDA(cudaDeviceSynchronize());
+  SBLAS_CUDA(cudaFree(stage));
+  *d_out = dst;
+  *ld_out = ld;
+  return 0;
+}
+
+template <typename T>
+static int dense_download(int gpu, const T* d_src, int64_t ld, int64_t second, int64_t dim,
+                          int32_t layout, T* h_dst) {
+  if (second <= 0 || dim <= 0) return 0;
+  SBLAS_CHECK(d_src && h_dst, "dense_download: null pointer");
+  SBLAS_ON_GPU(gpu);
+  const size_t bytes = sizeof(T) * (size_t)second * (size_t)dim;
+  if (layout == SBLAS_COL_MAJOR) {
+    SBLAS_CHECK(ld == second, "dense_download: col-major slices are contiguous (ld == rows)");
+    SBLAS_CUDA(cudaMemcpy(h_dst, d_src, bytes, cudaMemcpyDeviceToHost));
+    return 0;
+  }
+  T* stage = nullptr;
+  SBLAS_CUDA(cudaMalloc(&stage, bytes));
+  int rc = sizeof(T) == 8
+               ? sblas_transpose_f64(nullptr, (const double*)d_src, ld, second, dim, (double*)stage, second)
+               : sblas_transpose_f32(nullptr, (const float*)d_src, ld, second, dim, (float*)stage, second);
+  if (rc) return rc;
+  SBLAS_CUDA(cudaMemcpy(h_dst, stage, bytes, cudaMemcpyDeviceToHost));
+  SBLAS_CUDA(cudaFree(stage));
+  return 0;
+}
+
+}  // namespace sblas
+
+using namespace sblas;
+extern "C" {
+
+int sblas_host_alloc(size_t bytes, void** p) {
+  SBLAS_CHECK(p, "host_alloc: null out pointer");
+  *p = nullptr;
+  if (bytes == 0) bytes = 1;
+  if (has_device()) {
+    SBLAS_CUDA(cudaMallocHost(p, bytes));  // SAFE_ALOC_HOST, utility.h:122
+  } else {
+    // no driver (CPU-only host logic / partition tests): ordinary memory; no kernel can run anyway
+    SBLAS_CHECK(posix_memalign(p, 64, bytes) == 0, "host_alloc: out of memory (%zu bytes)", bytes);
+  }
+  return 0;
+}
+int sblas_host_free(void* p) {
+  if (!p) return 0;
+  if (has_device()) SBLAS_CUDA(cudaFreeHost(p)); else free(p);
+  return 0;
+}
+int sblas_dev_alloc(int gpu, size_t bytes, void** d_p) {
+  SBLAS_CHECK(d_p, "dev_alloc: null out pointer");
+  *d_p = nullptr;
+  SBLAS_ON_GPU(gpu);
+  SBLAS_CUDA(cudaMalloc(d_p, bytes ? bytes : 16));  // SAFE_ALOC_GPU, utility.h:86
+  return 0;
+}
+int sblas_dev_free(int gpu, void* d_p) {
+  if (!d_p) return 0;
+  SBLAS_ON_GPU(gpu);
+  SBLAS_CUDA(cudaFree(d_p));
+  return 0;
+}
+int sblas_copy_h2d(int gpu, void* d_dst, const void* h_src, size_t bytes) {
+  if (bytes == 0) return 0;
+  SBLAS_ON_GPU(gpu);
+  SBLAS_CUDA(cudaMemcpy(d_dst, h_src, bytes, cudaMemcpyHostToDevice));
+  return 0;
+}
+int sblas_copy_d2h(int gpu, void* h_dst, const void* d_src, size_t bytes) {
+  if (bytes == 0) return 0;
+  SBLAS_ON_GPU(gpu);
+  SBLAS_CUDA(cudaMemcpy(h_dst, d_src, bytes, cudaMemcpyDeviceToHost));
+  return 0;
+}
+int sblas_copy_d2d(int gpu, void* d_dst, const void* d_src, size_t bytes) {
+  if (bytes == 0) return 0;
+  SBLAS_ON_GPU(gpu);
+  SBLAS_CUDA(cudaMemcpy(d_dst, d_src, bytes, cudaMemcpyDeviceToDevice));
+  return 0;
+}
+int sblas_dev_memset(int gpu, void* d_p, int value, size_t bytes) {
+  if (bytes == 0) return 0;
+  SBLAS_ON_GPU(gpu);
+  SBLAS_CUDA(cudaMemset(d_p, value, bytes));
+  return 0;
+}
+int sblas_dev_sync(int gpu) {
+  SBLAS_ON_GPU(gpu);
+  SBLAS_CUDA(cudaDeviceSynchronize());
+  return 0;
+}
+
+int sblas_dense_upload_f64(int gpu, const double* h, int64_t second, int64_t dim, int32_t layout,
+                           double** d_out, int64_t* ld_out) {
+  return dense_upload<double>(gpu, h, second, dim, layout, d_out, ld_out);
+}
+int sblas_dense_upload_f32(int gpu, const float* h, int64_t second, int64_t dim, int32_t layout,
+                           float** d_out, int64_t* ld_out) {
+  return dense_upload<float>(gpu, h, second, dim, layout, d_out, ld_out);
+}
+int sblas_dense_download_f64(int gpu, const double* d, int64_t ld, int64_t second, int64_t dim,
+                             int32_t layout, double* h) {
+  return dense_download<double>(gpu, d, ld, second, dim, layout, h);
+}
+int sblas_dense_download_f32(int gpu, const float* d, int64_t ld, int64_t second, int64_t dim,
+                             int32_t layout, float* h) {
+  return dense_download<float>(gpu, d, ld, second, dim, layout, h);
+}
+
+// sblas_plan_create_i32 / sblas_axpby_* on a logical GPU (the classes of matrix.h never call
+// cudaSetDevice themselves)
+int sblas_plan_create_on(int gpu, int32_t rows, int64_t nnz, const int32_t* d_rowptr, sblasPlan_t* plan) {
+  SBLAS_ON_GPU(gpu);
+  return sblas_plan_create_i32(nullptr, rows, nnz, d_rowptr, plan);
+}
+int sblas_axpby_on(int gpu, int is_f64, void* d_v0, const void* d_v1, double alpha, double beta, int64_t n) {
+  SBLAS_ON_GPU(gpu);
+  return is_f64 ? sblas_axpby_f64(nullptr, (double*)d_v0, (const double*)d_v1, alpha, beta, n)
+                : sblas_axpby_f32(nullptr, (float*)d_v0, (const float*)d_v1, (float)alpha, (float)beta, n);
+}
+
+int sblas_scal_add_on(int gpu, int is_f64, void* d_v, double val, double beta, int64_t n) {
+  SBLAS_ON_GPU(gpu);
+  return is_f64 ? sblas_scal_add_f64(nullptr, (double*)d_v, val, beta, n)
+                : sblas_scal_add_f32(nullptr, (float*)d_v, (float)val, (float)beta, n);
+}
+
+// ---- managed memory (matrix_um.h) ---------------------------------------------------------------
+int sblas_managed_alloc(size_t bytes, void** p) {
+  SBLAS_CHECK(p, "managed_alloc: null out pointer");
+  *p = nullptr;
+  SBLAS_CHECK(has_device(), "managed_alloc: no CUDA device");
+  SBLAS_CUDA(cudaMallocManaged(p, bytes ? bytes : 16, cudaMemAttachGlobal));
+  return 0;
+}
+int sblas_managed_free(void* p) {
+  if (p) SBLAS_CUDA(cudaFree(p));
+  return 0;
+}
+int sblas_mem_advise(void* p, size_t bytes, int advice, int gpu) {
+  if (!p || bytes == 0) return 0;
+  cudaMemoryAdvise a;
+  switch (advice) {
+    case SBLAS_ADVISE_SET_READ_MOSTLY: a = cudaMemAdviseSetReadMostly; break;
+    case SBLAS_ADVISE_UNSET_READ_MOSTLY: a = cudaMemAdviseUnsetReadMostly; break;
+    case SBLAS_ADVISE_SET_PREFERRED_LOCATION: a = cudaMemAdviseSetPreferredLocation; break;
+    case SBLAS_ADVISE_UNSET_PREFERRED_LOCATION: a = cudaMemAdviseUnsetPreferredLocation; break;
+    case SBLAS_ADVISE_SET_ACCESSED_BY: a = cudaMemAdviseSetAccessedBy; break;
+    case SBLAS_ADVISE_UNSET_ACCESSED_BY: a = cudaMemAdviseUnsetAccessedBy; break;
+    default: set_error("mem_advise: unknown advice %d", advice); return 2;
+  }
+  const int dev = gpu < 0 ? cudaCpuDeviceId : sblas_device_of(gpu);
+  SBLAS_CUDA(cudaMemAdvise(p, bytes, a, dev));
+  return 0;
+}
+int sblas_mem_prefetch(void* p, size_t bytes, int gpu) {
+  if (!p || bytes == 0) return 0;
+  const int dev = gpu < 0 ? cudaCpuDeviceId : sblas_device_of(gpu);
+  if (gpu >= 0) {
+    SBLAS_ON_GPU(gpu);
+    SBLAS_CUDA(cudaMemPrefetchAsync(p, bytes, dev, nullptr));
+  } else {
+    SBLAS_CUDA(cudaMemPrefetchAsync(p, bytes, dev, nullptr));
+  }
+  return 0;
+}
+
+}  // extern "C"

@@ -35,11 +35,13 @@ __global__ void row_stats_kernel(const int32_t* __restrict__ rowptr, int32_t row
 
 // tile_row[b] = smallest r in [0, rows] with r*rw + rowptr[r] >= b*T  (b = 0..n_tiles)
 __global__ void tile_search_kernel(const int32_t* __restrict__ rowptr, int32_t rows, int32_t rw,
-                                   int32_t T, int32_t n_tiles, int32_t* __restrict__ tile_row) {
+                                   int32_t T, int32_t n_tiles, int32_t* __restrict__ tile_row,
+                                   int32_t* __restrict__ tile_nnz) {
   int32_t b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b > n_tiles) return;
   if (b == n_tiles) {
     tile_row[b] = rows;
+    tile_nnz[b] = rowptr[rows];
     return;
   }
   int64_t target = (int64_t)b * T;
@@ -50,6 +52,7 @@ __global__ void tile_search_kernel(const int32_t* __restrict__ rowptr, int32_t r
     if (f >= target) hi = mid; else lo = mid + 1;
   }
   tile_row[b] = lo;
+  tile_nnz[b] = rowptr[lo];
 }
 
 // stats[0] = max nnz of a tile, stats[1] = max rows of a tile
@@ -88,11 +91,12 @@ int plan_get_table(sblasPlan_st* plan, cudaStream_t stream, int32_t rw, int32_t 
   t.n_tiles = (int32_t)nt;
   int32_t* d_stats = nullptr;
   SBLAS_CUDA(cudaMalloc(&t.d_tile_row, sizeof(int32_t) * (size_t)(t.n_tiles + 1)));
+  SBLAS_CUDA(cudaMalloc(&t.d_tile_nnz, sizeof(int32_t) * (size_t)(t.n_tiles + 1)));
   SBLAS_CUDA(cudaMalloc(&d_stats, 2 * sizeof(int32_t)));
   SBLAS_CUDA(cudaMemsetAsync(d_stats, 0, 2 * sizeof(int32_t), stream));
   int blocks = (int)ceil_div(t.n_tiles + 1, 256);
   tile_search_kernel<<<blocks, 256, 0, stream>>>(plan->d_rowptr, plan->rows, rw, T, t.n_tiles,
-                                                 t.d_tile_row);
+                                                 t.d_tile_row, t.d_tile_nnz);
   SBLAS_LAUNCH_CHECK();
   tile_stats_kernel<<<blocks, 256, 0, stream>>>(plan->d_rowptr, t.d_tile_row, t.n_tiles, d_stats);
   SBLAS_LAUNCH_CHECK();
@@ -171,7 +175,7 @@ int sblas_plan_destroy(sblasPlan_t p) {
   int cur = 0;
   cudaGetDevice(&cur);
   cudaSetDevice(p->device);
-  for (TileTable& t : p->tables) cudaFree(t.d_tile_row);
+  for (TileTable& t : p->tables) { cudaFree(t.d_tile_row); if (t.d_tile_nnz) cudaFree(t.d_tile_nnz); }
   if (p->d_split_scratch) cudaFree(p->d_split_scratch);
   cudaSetDevice(cur);
   delete p;

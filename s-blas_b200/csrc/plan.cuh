@@ -22,6 +22,7 @@ struct TileTable {
   int32_t row_weight = 1;  // merge weight of one row
   int32_t n_tiles = 0;
   int32_t* d_tile_row = nullptr;  // [n_tiles + 1], first row of each tile; last = rows
+  int32_t* d_tile_nnz = nullptr;  // [n_tiles + 1], rowptr[tile_row[b]]: first nnz of each tile; last = nnz
   int32_t max_tile_nnz = 0;
   int32_t max_tile_rows = 0;
 };

@@ -22,8 +22,10 @@
 namespace sblas {
 
 constexpr int kSpmvBlock = 256;
-constexpr int kSpmvDefaultTile = 3072;
+constexpr int kSpmvDefaultTile = 3072;      // TILE / SPLIT
+constexpr int kSpmvPipeDefaultTile = 1536;  // PIPE: small tiles, 2 stages -> most resident CTAs (sweeps, profiles/)
 constexpr int kSpmvMaxSmem = 96 * 1024;
+constexpr int kSpmvPipeMaxRow = 4096;       // longest row PIPE stages whole (2 stages <= ~200 KB)
 
 template <typename T>
 struct RowSink {
@@ -38,6 +40,14 @@ struct RowSink {
     if ((flags & SBLAS_FLAG_HEAD_PARTIAL) && r == 0) { carry[0] = sum; return; }
     if ((flags & SBLAS_FLAG_TAIL_PARTIAL) && r == rows - 1) { carry[4] = sum; return; }
     T res = axpby_rn(alpha, sum, beta, y[r]);
+    y[r] = res;
+    for (int d = 0; d < out.n; ++d) out.ptr[d][r] = res;
+  }
+  // same, with the old y[r] already staged by the caller (pipelined kernel)
+  __device__ __forceinline__ void put_y(int32_t r, T sum, T yold) const {
+    if ((flags & SBLAS_FLAG_HEAD_PARTIAL) && r == 0) { carry[0] = sum; return; }
+    if ((flags & SBLAS_FLAG_TAIL_PARTIAL) && r == rows - 1) { carry[4] = sum; return; }
+    T res = axpby_rn(alpha, sum, beta, yold);
     y[r] = res;
     for (int d = 0; d < out.n; ++d) out.ptr[d][r] = res;
   }
@@ -182,6 +192,184 @@ spmv_tile_kernel(const int32_t* __restrict__ tile_row, const int32_t* __restrict
   reduce_rows_dispatch<T, BLOCK>(lanes, s_prod, s_rp, nrows, n0a, ts);
 }
 
+// ---- PIPE: persistent CTAs, NSTAGE-deep TMA-bulk staging of the tiles -------------------------
+// The TILE kernel above pays three dependent DRAM round trips per CTA (row pointers -> A
+// stream -> old y) with nothing in flight in between, so it sits near half of the HBM rate.
+// Here a CTA walks the tiles b = blockIdx.x, blockIdx.x + gridDim.x, ... and keeps the next
+// NSTAGE-1 tiles in flight while it reduces the current one.  Everything a tile needs is a
+// contiguous range known from the plan's {tile_row, tile_nnz} tables:
+//   col_idx[n0,n1), val[n0,n1)   one cp.async.bulk each for the 16-byte aligned middle
+//                                 (issued by one thread), <= 3-element heads/tails by LDGSTS;
+//   rowptr[r0..r1], y[r0,r1)     4/8-byte LDGSTS spread over the CTA;
+// and ONE mbarrier phase per stage collects all of it (expect_tx for the bulk bytes,
+// cp.async.mbarrier.arrive.noinc for the LDGSTS of every thread).  Products overwrite the
+// staged values in place, rows are reduced from shared memory exactly as in TILE.
+constexpr int kPipeHeaderBytes = 256;  // mbarriers + tile descriptors
+
+template <typename T>
+struct PipeStage {
+  T* val;        // [cap_nnz]  staged values, then products (index j - (n0 & ~3))
+  int32_t* col;  // [cap_nnz]
+  int32_t* rp;   // [cap_rows + 1]
+  T* y;          // [cap_rows]
+};
+
+template <typename T>
+__host__ __device__ inline size_t pipe_stage_bytes(int32_t cap_nnz, int32_t cap_rows) {
+  const size_t rp = ((size_t)(cap_rows + 1) * 4 + 15) & ~(size_t)15;
+  const size_t y = ((size_t)cap_rows * sizeof(T) + 15) & ~(size_t)15;
+  return (size_t)cap_nnz * (sizeof(T) + 4) + rp + y;  // cap_nnz is a multiple of 4
+}
+
+template <typename T>
+__device__ __forceinline__ PipeStage<T> pipe_stage(unsigned char* base, int s, int32_t cap_nnz,
+                                                   int32_t cap_rows) {
+  unsigned char* p = base + (size_t)s * pipe_stage_bytes<T>(cap_nnz, cap_rows);
+  PipeStage<T> st;
+  st.val = reinterpret_cast<T*>(p);
+  p += (size_t)cap_nnz * sizeof(T);
+  st.col = reinterpret_cast<int32_t*>(p);
+  p += (size_t)cap_nnz * 4;
+  st.rp = reinterpret_cast<int32_t*>(p);
+  p += ((size_t)(cap_rows + 1) * 4 + 15) & ~(size_t)15;
+  st.y = reinterpret_cast<T*>(p);
+  return st;
+}
+
+template <typename T>
+struct PipeSink {
+  const RowSink<T>& sink;
+  const T* s_y;
+  int32_t r0;
+  __device__ __forceinline__ void put(int i, T sum) const { sink.put_y(r0 + i, sum, s_y[i]); }
+};
+
+// Rows of a staged tile: G lanes per row read (col, val) pairs from shared memory (consecutive
+// lanes -> consecutive elements: conflict-free for G > 1; for G = 1 the stride is the row
+// length), gather x with U independent loads in flight per lane, and accumulate in CSR order
+// with separately rounded mul/add (G = 1: bit-identical to spmv.h:24-30), then shuffle-reduce.
+template <typename T, int G, int U, int BLOCK, typename Sink>
+__device__ __forceinline__ void consume_rows(const int32_t* __restrict__ s_col,
+                                             const T* __restrict__ s_val,
+                                             const int32_t* __restrict__ s_rp, int32_t nrows,
+                                             int32_t n0a, const T* __restrict__ x,
+                                             const Sink& sink) {
+  const int gl = threadIdx.x & (G - 1), gi = threadIdx.x / G;
+  for (int i0 = 0; i0 < nrows; i0 += BLOCK / G) {  // block-uniform trip count
+    const int i = i0 + gi;
+    const bool valid = i < nrows;
+    const int s = valid ? s_rp[i] - n0a : 0, e = valid ? s_rp[i + 1] - n0a : 0;
+    T sum = 0;
+    for (int j0 = s + gl; j0 < e; j0 += G * U) {
+      T vv[U], xx[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int j = j0 + u * G;
+        if (j < e) {
+          vv[u] = s_val[j];
+          xx[u] = __ldg(x + s_col[j]);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        if (j0 + u * G < e) sum = add_rn(sum, mul_rn(vv[u], xx[u]));
+    }
+    if (G > 1) {
+#pragma unroll
+      for (int m = G / 2; m > 0; m >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, m);
+    }
+    if (valid && gl == 0) sink.put(i, sum);
+  }
+}
+
+template <typename T, int BLOCK, int NSTAGE, int G>
+__global__ void __launch_bounds__(BLOCK)
+spmv_pipe_kernel(const int32_t* __restrict__ tile_row, const int32_t* __restrict__ tile_nnz,
+                 int32_t n_tiles, const int32_t* __restrict__ rowptr,
+                 const int32_t* __restrict__ colidx, const T* __restrict__ val,
+                 const T* __restrict__ x, RowSink<T> sink, int32_t cap_nnz, int32_t cap_rows) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw);     // [NSTAGE <= 8]
+  int4* descs = reinterpret_cast<int4*>(smem_raw + 64);        // [NSTAGE] tile in each stage
+  unsigned char* stages = smem_raw + kPipeHeaderBytes;
+  const int tid = threadIdx.x;
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < NSTAGE; ++s) mbar_init(&bars[s], BLOCK + 1);
+    mbar_fence_init();
+  }
+  __syncthreads();
+  const int my_tiles = ((int)n_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+
+  // descriptor of my i-th tile: (r0, r1, n0, n1)
+  auto load_desc = [&](int i) -> int4 {
+    if (i >= my_tiles) return make_int4(0, 0, 0, 0);
+    const int64_t b = (int64_t)blockIdx.x + (int64_t)i * gridDim.x;
+    return make_int4(__ldg(tile_row + b), __ldg(tile_row + b + 1), __ldg(tile_nnz + b),
+                     __ldg(tile_nnz + b + 1));
+  };
+  // start every load of tile i (descriptor d) into stage i % NSTAGE
+  auto issue = [&](int i, const int4& d) {
+    if (i >= my_tiles) return;
+    const int s = i % NSTAGE;
+    uint64_t* bar = &bars[s];
+    const PipeStage<T> st = pipe_stage<T>(stages, s, cap_nnz, cap_rows);
+    const int32_t r0 = d.x, nrows = d.y - d.x, n0 = d.z, n1 = d.w;
+    const int32_t n0a = n0 & ~3;
+    const int32_t m0 = min((n0 + 3) & ~3, n1);  // aligned middle [m0, m1)
+    const int32_t m1 = max(n1 & ~3, m0);
+    if (tid == 0) {
+      const uint32_t cnt = (uint32_t)(m1 - m0);
+      descs[s] = d;  // published to the CTA by the release/acquire of the mbarrier phase
+      mbar_arrive_expect_tx(bar, cnt * (uint32_t)(sizeof(T) + 4));
+      if (cnt) {
+        bulk_g2s(st.col + (m0 - n0a), colidx + m0, cnt * 4u, bar);
+        bulk_g2s(st.val + (m0 - n0a), val + m0, cnt * (uint32_t)sizeof(T), bar);
+      }
+    } else if (tid >= 32 && tid < 32 + (m0 - n0)) {  // head, <= 3 elements
+      const int32_t j = n0 + (tid - 32);
+      cp_async4(st.col + (j - n0a), colidx + j);
+      cp_async_elem(st.val + (j - n0a), val + j);
+    } else if (tid >= 64 && tid < 64 + (n1 - m1)) {  // tail, <= 3 elements
+      const int32_t j = m1 + (tid - 64);
+      cp_async4(st.col + (j - n0a), colidx + j);
+      cp_async_elem(st.val + (j - n0a), val + j);
+    }
+    for (int i2 = tid; i2 <= nrows; i2 += BLOCK) cp_async4(st.rp + i2, rowptr + r0 + i2);
+    for (int i2 = tid; i2 < nrows; i2 += BLOCK) cp_async_elem(st.y + i2, sink.y + r0 + i2);
+    cp_async_mbar_arrive_noinc(bar);
+  };
+
+  int4 d_next = load_desc(0);
+#pragma unroll 1
+  for (int i = 0; i < NSTAGE - 1; ++i) {  // prologue: tiles 0 .. NSTAGE-2
+    const int4 d = d_next;
+    d_next = load_desc(i + 1);
+    issue(i, d);
+  }
+  // d_next is now the descriptor of tile NSTAGE-1
+#pragma unroll 1
+  for (int i = 0; i < my_tiles; ++i) {
+    {
+      const int4 d = d_next;
+      d_next = load_desc(i + NSTAGE);
+      issue(i + NSTAGE - 1, d);
+    }
+    const int s = i % NSTAGE;
+    const PipeStage<T> st = pipe_stage<T>(stages, s, cap_nnz, cap_rows);
+    mbar_wait(&bars[s], (uint32_t)(i / NSTAGE) & 1u);
+    const int4 d = descs[s];
+    const int32_t r0 = d.x, nrows = d.y - d.x, n0 = d.z, n1 = d.w;
+    if (nrows > 0) {
+      // rows straight from the staged tile: G lanes per row, U gathers in flight per lane
+      const PipeSink<T> ps{sink, st.y, r0};
+      consume_rows<T, G, (G == 1 ? 8 : 4), BLOCK>(st.col, st.val, st.rp, nrows, n0 & ~3, x, ps);
+    }
+    fence_proxy_async_smem();  // my generic-proxy accesses of this stage precede its next bulk fill
+    __syncthreads();
+  }
+}
+
 // ---- VECTOR: G lanes per row, straight from global memory ----------------------------------
 template <typename T, int G, int BLOCK, bool FMA>
 __global__ void __launch_bounds__(BLOCK)
@@ -309,11 +497,27 @@ static int pow2_lanes(double avg) {
   return l;
 }
 
+static int pow2_lanes_pipe(double avg) {
+  return avg <= 6 ? 1 : avg <= 12 ? 2 : avg <= 24 ? 4 : avg <= 48 ? 8 : avg <= 96 ? 16 : 32;
+}
+
+template <typename T>
+static const void* pipe_kernel_ptr(int stages, int G) {
+#define SBLAS_PK(NS, GG) (const void*)spmv_pipe_kernel<T, kSpmvBlock, NS, GG>
+#define SBLAS_PKG(NS)                                                                          \
+  (G <= 1 ? SBLAS_PK(NS, 1) : G == 2 ? SBLAS_PK(NS, 2) : G == 4 ? SBLAS_PK(NS, 4)               \
+   : G == 8 ? SBLAS_PK(NS, 8) : G == 16 ? SBLAS_PK(NS, 16) : SBLAS_PK(NS, 32))
+  return stages <= 2 ? SBLAS_PKG(2) : stages == 3 ? SBLAS_PKG(3) : SBLAS_PKG(4);
+#undef SBLAS_PKG
+#undef SBLAS_PK
+}
+
 template <typename T>
 static int resolve_variant(const sblasPlan_st* plan, const sblasOpts* o, int32_t tile) {
   if (o && o->variant != SBLAS_VARIANT_AUTO) return o->variant;
   if (!plan) return SBLAS_SPMV_VECTOR;
-  return plan->max_row_nnz <= tile / 2 ? SBLAS_SPMV_TILE : SBLAS_SPMV_SPLIT;
+  (void)tile;
+  return plan->max_row_nnz <= kSpmvPipeMaxRow ? SBLAS_SPMV_PIPE : SBLAS_SPMV_SPLIT;
 }
 
 template <typename T>
@@ -343,7 +547,7 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
   sink.flags = flags;
   sink.alpha = alpha;
   sink.beta = beta;
-  const int32_t tile = (o && o->tile > 0) ? o->tile : kSpmvDefaultTile;
+  int32_t tile = (o && o->tile > 0) ? o->tile : kSpmvDefaultTile;
   sblasPlan_st* eph = nullptr;
   int variant = resolve_variant<T>(plan, o, tile);
   if (!plan && variant != SBLAS_SPMV_VECTOR) {
@@ -353,7 +557,48 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
   if (plan) SBLAS_CHECK(plan->rows == rows && plan->nnz == nnz, "spmv: plan does not match matrix");
   const bool vec = aligned16(ci) && aligned16(v);
   int rc = 0;
-  if (variant == SBLAS_SPMV_TILE) {
+  if (variant == SBLAS_SPMV_PIPE && !(o && o->tile > 0))  // every row must fit a tile's staging buffer
+    tile = std::max<int32_t>(kSpmvPipeDefaultTile, std::min<int32_t>(2 * kSpmvPipeMaxRow, (2 * plan->max_row_nnz + 511) & ~511));
+  if (variant == SBLAS_SPMV_PIPE) {
+    // persistent TMA-staged tiles; needs 16-byte aligned col_idx / val (else: TILE)
+    const TileTable* tt = nullptr;
+    if (!vec) {
+      variant = SBLAS_SPMV_TILE;
+    } else if ((rc = plan_get_table(plan, st, 1, tile, &tt)) == 0) {
+      const int32_t cap_nnz = (tt->max_tile_nnz + 8 + 3) & ~3;  // + head alignment slack
+      const int32_t cap_rows = tt->max_tile_rows + 1;
+      int stages = (o && o->stages > 0) ? o->stages : 2;
+      stages = std::min(std::max(stages, 2), 4);
+      auto smem_for = [&](int ns) { return (size_t)kPipeHeaderBytes + ns * pipe_stage_bytes<T>(cap_nnz, cap_rows); };
+      while (stages > 2 && smem_for(stages) > 110 * 1024) --stages;  // keep >= 2 CTAs per SM
+      if (smem_for(stages) > 200 * 1024) {
+        variant = SBLAS_SPMV_SPLIT;  // a row too long for the staging buffers: cut rows instead
+      } else {
+        const int smem = (int)smem_for(stages);
+        // lanes per row from the mean row length (one instantiation per launch keeps the
+        // kernel small: ~50 registers instead of 160 with an in-kernel switch)
+        int G = (o && o->lanes > 0) ? o->lanes : pow2_lanes_pipe(rows ? (double)(nnz / rows) : 0.0);  // integer mean, as the per-tile rule of TILE
+        const void* kern = pipe_kernel_ptr<T>(stages, G);
+        int per_sm = 0;
+        if ((rc = set_smem_once<T>(kern, smem)) == 0) {
+          cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kSpmvBlock, smem);
+          if (e != cudaSuccess || per_sm < 1) { set_error("spmv pipe: occupancy query: %s", cudaGetErrorString(e)); rc = 1; }
+        }
+        if (rc == 0) {
+          int n_sm = kNumSM;
+          cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, plan->device);
+          const int grid = std::min<int>(tt->n_tiles, n_sm * per_sm);
+          void* args[] = {(void*)&tt->d_tile_row, (void*)&tt->d_tile_nnz, (void*)&tt->n_tiles, (void*)&rp,
+                          (void*)&ci, (void*)&v, (void*)&x, (void*)&sink, (void*)&cap_nnz,
+                          (void*)&cap_rows};
+          cudaError_t e = cudaLaunchKernel(kern, dim3(grid), dim3(kSpmvBlock), args, smem, st);
+          ++g_launches;
+          if (e != cudaSuccess) { set_error("spmv pipe launch: %s", cudaGetErrorString(e)); rc = 3; }
+        }
+      }
+    }
+  }
+  if (rc == 0 && variant == SBLAS_SPMV_TILE) {
     const TileTable* tt = nullptr;
     if ((rc = plan_get_table(plan, st, 1, tile, &tt)) == 0) {
       const int32_t cap = (tt->max_tile_nnz + 9) & ~3;
@@ -418,7 +663,7 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
                                   : launch_vector<T, kSpmvBlock, false>(st, lanes, rows, rp, ci, v, x, sink);
   }
   if (rc == 0 && variant != SBLAS_SPMV_TILE && variant != SBLAS_SPMV_SPLIT &&
-      variant != SBLAS_SPMV_VECTOR) {
+      variant != SBLAS_SPMV_VECTOR && variant != SBLAS_SPMV_PIPE) {
     set_error("spmv: unknown variant %d", variant);
     rc = 2;
   }

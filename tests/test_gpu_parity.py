@@ -59,7 +59,7 @@ MATS = {
 
 @pytest.mark.parametrize("dtype", [np.float64, np.float32])
 @pytest.mark.parametrize("mat", list(MATS))
-@pytest.mark.parametrize("variant", ["auto", "tile", "vector", "split", "noplan"])
+@pytest.mark.parametrize("variant", ["auto", "tile", "pipe", "pipe2", "vector", "split", "noplan"])
 def test_spmv_vs_oracle(sblas, dev, oracle, dtype, mat, variant):
     import torch
     K = sblas.kernels
@@ -73,8 +73,10 @@ def test_spmv_vs_oracle(sblas, dev, oracle, dtype, mat, variant):
     ref = oracle.spmv(rp, ci, v, x, y0.copy(), alpha, beta)
     drp, dci, dv, dx, dy = (_t(dev, a) for a in (rp, ci, v, x, y0))
     plan = None if variant == "noplan" else K.Plan(drp, len(ci))
-    var = dict(auto=0, noplan=0, tile=sblas.SPMV_TILE, vector=sblas.SPMV_VECTOR, split=sblas.SPMV_SPLIT)[variant]
-    opts = sblas.make_opts(variant=var, tile=512 if variant in ("tile", "split") else 0)
+    var = dict(auto=0, noplan=0, tile=sblas.SPMV_TILE, vector=sblas.SPMV_VECTOR, split=sblas.SPMV_SPLIT,
+               pipe=sblas.SPMV_PIPE, pipe2=sblas.SPMV_PIPE)[variant]
+    opts = sblas.make_opts(variant=var, tile={"tile": 512, "split": 512, "pipe": 320, "pipe2": 3072}.get(variant, 0),
+                           stages={"pipe": 4, "pipe2": 2}.get(variant, 0))
     K.spmv(drp, dci, dv, dx, dy, alpha, beta, plan=plan, opts=opts)
     torch.cuda.synchronize()
     bound = _row_bound(oracle, rp, ci, v, x, alpha, beta, y0)
@@ -140,7 +142,7 @@ def test_spmv_partials_and_replicas(sblas, dev, oracle):
     x, y0 = rng.random(500), rng.random(500)
     ref = oracle.spmv(rp, ci, v, x, y0.copy(), 2.0, 0.5)
     raw = oracle.spmv(rp, ci, v, x, np.zeros(500), 1.0, 0.0)
-    for var in (sblas.SPMV_TILE, sblas.SPMV_VECTOR, sblas.SPMV_SPLIT):
+    for var in (sblas.SPMV_TILE, sblas.SPMV_VECTOR, sblas.SPMV_SPLIT, sblas.SPMV_PIPE):
         drp, dci, dv, dx, dy = (_t(dev, a) for a in (rp, ci, v, x, y0))
         rep = torch.full((500,), -7.0, dtype=torch.float64, device=dev)
         carry = torch.zeros(8, dtype=torch.float64, device=dev)

@@ -1,18 +1,15 @@
 #!/bin/bash
-# First GPU pass: parity tests, smoke, bench, variant sweeps, ncu launch list.
+# Second GPU pass: parity tests, variant sweeps on every workload, ncu full capture of the c2 SpMV kernel.
 mkdir -p gpurun_out
-nvidia-smi --query-gpu=name,memory.total,clocks.max.sm --format=csv > gpurun_out/gpu.txt 2>&1
-timeout 1500 python -m pytest tests -m gpu -q -x --timeout=300 -p no:cacheprovider > gpurun_out/pytest_gpu.log 2>&1
+timeout 900 python -m pytest tests -m gpu -q --timeout=300 -p no:cacheprovider > gpurun_out/pytest_gpu.log 2>&1
 echo "pytest exit $?" >> gpurun_out/pytest_gpu.log
-tail -30 gpurun_out/pytest_gpu.log
-timeout 300 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "smoke exit $?" >> gpurun_out/smoke.log; tail -3 gpurun_out/smoke.log
-timeout 600 python bench.py > gpurun_out/bench_c2.json 2> gpurun_out/bench_c2.err; echo "bench exit $?"; cat gpurun_out/bench_c2.json; tail -5 gpurun_out/bench_c2.err
-timeout 600 python tools/sweep.py --workload c2 --reps 20 > gpurun_out/sweep_c2.log 2>&1; tail -40 gpurun_out/sweep_c2.log
-timeout 600 python tools/sweep.py --workload b32 --reps 10 > gpurun_out/sweep_b32.log 2>&1
-timeout 600 python tools/sweep.py --workload c3v --reps 10 > gpurun_out/sweep_c3v.log 2>&1
-timeout 600 python tools/sweep.py --workload c4 --reps 10 > gpurun_out/sweep_c4.log 2>&1
-timeout 900 python tools/sweep.py --workload c3 --reps 3 > gpurun_out/sweep_c3.log 2>&1
-timeout 900 python tools/sweep.py --workload c5 --reps 3 > gpurun_out/sweep_c5.log 2>&1
-timeout 300 python bench.py --steps 20 --warmup 3 --no-cpu --no-e2e > gpurun_out/plain.log 2>&1 && \
-timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file gpurun_out/launches_c2.csv python bench.py --steps 20 --warmup 3 --no-cpu --no-e2e > gpurun_out/ncu_list.log 2>&1
+tail -5 gpurun_out/pytest_gpu.log
+timeout 600 python tools/sweep.py --workload b32 --reps 10 > gpurun_out/sweep_b32.log 2>&1; echo "b32 $?"
+timeout 600 python tools/sweep.py --workload c3v --reps 10 > gpurun_out/sweep_c3v.log 2>&1; echo "c3v $?"
+timeout 600 python tools/sweep.py --workload c4 --reps 10 > gpurun_out/sweep_c4.log 2>&1; echo "c4 $?"
+timeout 900 python tools/sweep.py --workload c3 --reps 3 > gpurun_out/sweep_c3.log 2>&1; echo "c3 $?"
+timeout 900 python tools/sweep.py --workload c5 --reps 3 > gpurun_out/sweep_c5.log 2>&1; echo "c5 $?"
+timeout 300 python bench.py --steps 5 --warmup 3 --no-cpu --no-e2e > gpurun_out/plain.log 2>&1 && \
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:spmv_tile -s 3 -c 2 -o gpurun_out/prof_c2_spmv -f python bench.py --steps 5 --warmup 3 --no-cpu --no-e2e > gpurun_out/ncu_full.log 2>&1
+echo "ncu $?"
 echo finished

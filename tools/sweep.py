@@ -25,6 +25,8 @@ def main():
     ap.add_argument("--scale-down", type=int, default=1)
     ap.add_argument("--grid", default="default")
     ap.add_argument("--out", default=None)
+    ap.add_argument("--dirty-flush", action="store_true")
+    ap.add_argument("--only", type=int, default=None, help="only this variant")
     args = ap.parse_args()
     import torch
     import __graft_entry__ as ge
@@ -44,17 +46,22 @@ def main():
     xB = pkg.synth.fill_uniform(torch.empty(cols * k, dtype=td, device=dev), stream_id=11)
     yC = torch.ones(rows * k, dtype=td, device=dev)
     flush = torch.empty(2 * bench.L2_BYTES // 4, dtype=torch.int32, device=dev)
+    flush_rd = torch.ones_like(flush)
     ab = bench.algorithmic_bytes(wl["op"], rows, cols, nnz, k, esz)
     if wl["op"] == "spmv":
         grid = [dict(variant=0)]
         grid += [dict(variant=pkg.SPMV_TILE, tile=t, lanes=l) for t in (1024, 1536, 2048, 3072, 4096, 6144, 8192)
                  for l in ((0,) if args.grid == "default" else (0, 1, 2, 4, 8, 16, 32))]
         grid += [dict(variant=pkg.SPMV_SPLIT, tile=t) for t in (2048, 3072, 4096, 8192)]
+        grid += [dict(variant=pkg.SPMV_PIPE, tile=t, stages=st, lanes=l) for t in (1536, 2048, 3072, 4096, 6144, 8192) for st in (2, 3, 4)
+                 for l in ((0,) if args.grid == 'default' else (0, 1, 2, 4, 8, 16))]
         grid += [dict(variant=pkg.SPMV_VECTOR, lanes=l, flags=f) for l in (1, 2, 4, 8, 16, 32) for f in (0, 1)]
     else:
         grid = [dict(tile=t, flags=f, lanes=l) for t in (256, 512, 1024, 2048, 4096, 16384) for f in (0, 1)
                 for l in ((0,) if args.grid == "default" else (0, 32))]
     res = []
+    if args.only is not None:
+        grid = [g for g in grid if g.get('variant') == args.only]
     for g in grid:
         o = pkg.make_opts(**g)
 
@@ -70,6 +77,8 @@ def main():
             ts = []
             for _ in range(args.reps):
                 flush.zero_()
+                if not args.dirty_flush:
+                    flush_rd.sum()   # leave L2 full of CLEAN lines (no write-backs billed to the kernel)
                 a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 a.record()
                 run()
