@@ -16,6 +16,7 @@ Workloads (BASELINE.json `configs`):
   c4   R-MAT scale 23, edge factor 16, fp32 SpMV                    (configs[3])
   c5   banded 2^21 x 64/row, fp64 SpMM k=256, method 1              (configs[4])
   b32  banded 2^24 x 32/row, fp64 SpMV (structured 16M x 32 counterpart of c3v)
+  b32m banded 2^24 x 32/row, fp64 SpMM k=64 (structured 16M x 32 counterpart of c3)
 --impl reference times the reference's own CPU implementation (oracle/_ref, else the oracle
 port) on the host cores, on a bounded row sample of the same workload.
 """
@@ -63,6 +64,8 @@ WORKLOADS = {
                name="synthetic banded CSR, 2M rows x 64 nnz/row, fp64 SpMM k=256, method 1"),
     "b32": dict(op="spmv", dtype="f64", gen="banded", rows=1 << 24, bw=32,
                 name="synthetic banded CSR, 16M rows x 32 nnz/row, fp64 SpMV"),
+    "b32m": dict(op="spmm", dtype="f64", gen="banded", rows=1 << 24, bw=32, k=64, method=2,
+                 name="synthetic banded CSR, 16M rows x 32 nnz/row, fp64 SpMM k=64, method 2"),
 }
 
 
@@ -94,7 +97,7 @@ def gather_bytes(op, rows, cols, nnz, k, esize):
 class ClockSampler(threading.Thread):
     """Samples SM clock / throttle reasons of one GPU while the timed region runs."""
 
-    def __init__(self, index, period=0.02):
+    def __init__(self, index, period=0.004):
         super().__init__(daemon=True)
         self.index, self.period = index, period
         self.samples, self.reasons, self.max_mhz = [], set(), None
@@ -193,6 +196,8 @@ def run_ours(args, wl_key):
     cfg_extra = {}
     if world == 1:
         plan = K.Plan(rp, nnz)
+        if op == "spmm":
+            cfg_extra["rowblocks(R, blocks, fill)"] = plan.build_rowblocks(ci, v)   # part of sync2gpu
         ld = k
         xB = pkg.synth.fill_uniform(torch.empty(cols * ld, dtype=tdtype, device=dev), stream_id=11)
         yC = torch.ones(rows * ld, dtype=tdtype, device=dev)
@@ -211,6 +216,7 @@ def run_ours(args, wl_key):
         avg, dims = K.dense_split(k, world)
         kk = int(dims[rank])
         plan = K.Plan(rp, nnz)
+        cfg_extra["rowblocks(R, blocks, fill)"] = plan.build_rowblocks(ci, v)
         ld = kk
         xB = pkg.synth.fill_uniform(torch.empty(cols * ld, dtype=tdtype, device=dev), stream_id=11 + rank)
         yC = torch.ones(rows * ld, dtype=tdtype, device=dev)
@@ -262,9 +268,9 @@ def run_ours(args, wl_key):
             dist.barrier()
             torch.cuda.synchronize()
 
-    def timed(fn, steps):
-        """sum of per-step device times (CUDA events on the launching stream), L2 flushed
-        between steps outside the event pairs"""
+    def timed_flushed(fn, steps):
+        """per-step device times (CUDA events on the launching stream), L2 flushed between
+        steps outside the event pairs"""
         ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
               for _ in range(steps)]
         for a, b in ev:
@@ -275,6 +281,21 @@ def run_ours(args, wl_key):
             b.record()
         torch.cuda.synchronize()
         return [a.elapsed_time(b) for a, b in ev]
+
+    def timed_region(fn, steps):
+        """exactly `steps` steps back to back between one event pair (inputs larger than L2: every
+        step streams its operands from HBM again, no flush needed)"""
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(steps):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        return [a.elapsed_time(b) / steps] * steps
+
+    abytes = algorithmic_bytes(op, loc_rows, cols, loc_nnz, loc_k, esz)   # this rank's launch
+    big = abytes > 2 * L2_BYTES        # per-rank operands at least twice the L2: no flush needed
+    timed = timed_region if big else timed_flushed
 
     L = pkg._lib.lib()
     for _ in range(max(args.warmup, 3)):
@@ -289,16 +310,15 @@ def run_ours(args, wl_key):
     launches = int(L.sblas_launch_count() - n0)
     # kernel-only duration (no exchange) for the roofline; same as `ms` when there is no stitch
     ms_k = ms if step is step_compute else timed(step_compute, args.steps)
+    barrier()
     sampler.active = False
-    # back-to-back launches, no flush in between (reported for information only)
-    torch.cuda.synchronize()
-    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    a.record()
-    for _ in range(args.steps):
-        step_compute()
-    b.record()
-    torch.cuda.synchronize()
-    ms_b2b = a.elapsed_time(b) / args.steps
+    # the other protocol, for information (flushed per-step when the headline is back-to-back and
+    # vice versa); single GPU only (per-step events across unsynchronised ranks would time skew)
+    ms_other = None
+    if world == 1:
+        ms_other = float(np.median((timed_flushed if big else timed_region)(step_compute, min(args.steps, 50))))
+    if world > 1 and getattr(opx, "status", None) is not None and int(opx.status.item()) != 0:
+        raise SystemExit("peer barrier timed out waiting for rank %d" % (int(opx.status.item()) - 1))
 
     tot_ms = float(np.sum(ms))
     tot_k_ms = float(np.sum(ms_k))
@@ -309,7 +329,6 @@ def run_ours(args, wl_key):
     flops_step = 2.0 * nnz * k                       # whole job (all ranks)
     value = flops_step * args.steps / (tot_ms * 1e-3) / 1e9
     peak, peak_src = measured_peaks()
-    abytes = algorithmic_bytes(op, loc_rows, cols, loc_nnz, loc_k, esz)   # this rank's launch
     dur_s = tot_k_ms * 1e-3 / args.steps
     achieved = abytes / dur_s / 1e9
 
@@ -356,10 +375,12 @@ def run_ours(args, wl_key):
             "dtype": wl["dtype"], "data": "synthetic",
             "config": dict({"workload": wl_key + ": " + wl["name"], "rows": rows, "cols": cols,
                             "nnz": nnz, "k": k, "alpha": 1.0, "beta": 1.0, "index": "int32",
-                            "timing": "CUDA events per step on the launching stream; L2 flushed "
-                                      "(%d MiB memset + clean read sweep of a second buffer) between steps; inputs %s L2" % (
-                                          2 * L2_BYTES >> 20, "larger than" if abytes > L2_BYTES else "smaller than"),
-                            "ms_per_step_back_to_back_no_flush": ms_b2b,
+                            "timing": ("CUDA events around the K back-to-back steps on the launching stream; no L2 "
+                                       "flush: every rank's operands (%.0f MB) are larger than 2x the 126 MB L2" % (abytes / 1e6))
+                            if big else
+                            ("CUDA events per step on the launching stream; L2 flushed (%d MiB memset + clean "
+                             "read sweep of a second buffer) between steps" % (2 * L2_BYTES >> 20)),
+                            "ms_per_step_other_protocol": ms_other,
                             "wall_ms_timed_region": wall_ms,
                             "ms_per_step_min": float(np.min(ms)), "ms_per_step_median": float(np.median(ms))},
                            **cfg_extra),
@@ -572,7 +593,7 @@ def main():
     wl_key = args.workload or "c2"
     heavy = WORKLOADS[wl_key]["op"] == "spmm"
     if args.steps is None:
-        args.steps = 20 if heavy else 200
+        args.steps = 20 if heavy else 1000
     if args.warmup is None:
         args.warmup = 3 if heavy else 20
     if args.impl == "reference":

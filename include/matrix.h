@@ -187,6 +187,9 @@ class CsrSparseMatrix {
     SBLAS_SAFE_CALL(sblas_copy_h2d((int)i, csrVal_gpu[i], v, n_nz * sizeof(DataType)));
     SBLAS_SAFE_CALL(sblas_plan_create_on((int)i, (int32_t)(n_rp - 1), (int64_t)n_nz,
                                          (const int32_t*)csrRowPtr_gpu[i], &plan_gpu[i]));
+    /* SpMM row-block mirror of this GPU's rows (kept only for structured inputs, sblas_b200.h) */
+    SBLAS_SAFE_CALL(sblas_plan_build_rowblocks_on((int)i, sizeof(DataType) == 8, plan_gpu[i],
+                                                  (const int32_t*)csrColIdx_gpu[i], csrVal_gpu[i]));
   }
   void release_gpu_() {
     if (plan_gpu != NULL) {

@@ -53,7 +53,10 @@ enum {
   SBLAS_SPMV_PIPE = 4,    /* TILE's tiles walked by persistent CTAs; col_idx/val/rowptr/y of the next
                              tiles staged by TMA bulk copies + LDGSTS behind mbarriers (AUTO's choice) */
   SBLAS_SPMM_ROWMAJOR = 1, /* internal row-major B/C: one lane group per A row, 128-bit B gathers */
-  SBLAS_SPMM_COLMAJOR = 2  /* native col-major B/C (the reference's host layout), no transposes */
+  SBLAS_SPMM_COLMAJOR = 2, /* native col-major B/C (the reference's host layout), no transposes */
+  SBLAS_SPMM_ROWBLOCK = 3  /* row-major B/C on the plan's R x 1 row-block mirror of A: one B load feeds
+                              up to R adjacent rows (structured inputs); AUTO takes it when the plan
+                              holds the mirror (sblas_plan_build_rowblocks_*) */
 };
 enum {
   SBLAS_FLAG_FMA = 1,          /* allow fused multiply-add (default: separately rounded mul/add
@@ -121,6 +124,18 @@ typedef struct sblasCsrStats {
 SBLAS_API int sblas_plan_create_i32(void* stream, int32_t rows, int64_t nnz,
                                     const int32_t* d_rowptr, sblasPlan_t* plan);
 SBLAS_API int sblas_plan_stats(sblasPlan_t plan, sblasCsrStats* out);
+/* Row-block mirror of A for SpMM ("matrix.h device CSR layout", built inside
+ * CsrSparseMatrix::sync2gpu next to the CSR arrays of matrix.h:376-387): R (= 4) consecutive rows
+ * form a block row, every distinct column of a block row becomes one block {col, presence mask,
+ * R values}.  The arrays are only kept when fill = nnz / (blocks * R) >= 0.5; otherwise only the
+ * statistic is recorded and SpMM stays on the CSR kernel.  The mirror holds a COPY of the values:
+ * rebuild it after changing d_val.  d_colidx / d_val: the same device arrays later passed to
+ * sblas_spmm_csr_*.  R = 0 picks the default; a negative R keeps the mirror whatever the fill. */
+SBLAS_API int sblas_plan_build_rowblocks_f64(void* stream, sblasPlan_t plan, const int32_t* d_colidx,
+                                             const double* d_val, int32_t R);
+SBLAS_API int sblas_plan_build_rowblocks_f32(void* stream, sblasPlan_t plan, const int32_t* d_colidx,
+                                             const float* d_val, int32_t R);
+SBLAS_API int sblas_plan_rowblock_stats(sblasPlan_t plan, int32_t* R, int64_t* n_blocks, double* fill);
 SBLAS_API int sblas_plan_destroy(sblasPlan_t plan);
 
 /* ---- single-device kernels ---------------------------------------------------------- */
@@ -193,6 +208,8 @@ SBLAS_API int sblas_plan_create_on(int gpu, int32_t rows, int64_t nnz, const int
                                    sblasPlan_t* plan);
 SBLAS_API int sblas_axpby_on(int gpu, int is_f64, void* d_v0, const void* d_v1, double alpha,
                              double beta, int64_t n);
+SBLAS_API int sblas_plan_build_rowblocks_on(int gpu, int is_f64, sblasPlan_t plan, const int32_t* d_colidx,
+                                            const void* d_val);
 SBLAS_API int sblas_scal_add_on(int gpu, int is_f64, void* d_v, double val, double beta, int64_t n);
 /* DenseMatrix::sync2gpu / sync2cpu for one GPU's slice (matrix.h:541-570, :595-612).  h is the
  * host slice: `dim` leading-dimension lines of `second` contiguous elements each (for the
@@ -304,6 +321,18 @@ SBLAS_API int sblas_ipc_alloc(size_t bytes, void** d_ptr, unsigned char handle[6
 SBLAS_API int sblas_ipc_open(const unsigned char handle[64], void** d_ptr);
 SBLAS_API int sblas_ipc_close(void* d_ptr);
 SBLAS_API int sblas_ipc_free(void* d_ptr);
+
+/* Device-side barrier between the ranks of one node (one process per GPU), enqueued on `stream`:
+ * rank r stores `epoch` into slot r of every peer's flag array (d_peer_flags[t] = rank t's array
+ * of >= world int32, zero-initialised, mapped with sblas_ipc_open; entry [rank] = the local array)
+ * and waits until all slots of its own array reach `epoch`.  Because the flag stores follow the
+ * SpMV/SpMM kernel in stream order, the wait returning means every peer's rows are in the local
+ * replica: this completes the peer-store stitch with no host synchronisation and no collective
+ * (the reference needs ncclAllReduce + two OpenMP barriers here, spmv.h:108-120).  Epochs must
+ * increase by 1 per call on every rank.  A wait longer than ~2 s writes 1+peer into *d_status
+ * (may be NULL) and returns instead of hanging.  At most 15 ranks. */
+SBLAS_API int sblas_peer_barrier(void* stream, int rank, int world, int32_t* d_local_flags,
+                                 void* const* d_peer_flags, int32_t epoch, int32_t* d_status);
 
 /* Carry fix-up for rows shared between neighbouring segments (used by the multi-process
  * path too): for each of the n_shared rows, out[row] = beta*out[row] + alpha*sum(carries),

@@ -193,6 +193,12 @@ int sblas_axpby_on(int gpu, int is_f64, void* d_v0, const void* d_v1, double alp
                 : sblas_axpby_f32(nullptr, (float*)d_v0, (const float*)d_v1, (float)alpha, (float)beta, n);
 }
 
+int sblas_plan_build_rowblocks_on(int gpu, int is_f64, sblasPlan_t plan, const int32_t* d_colidx, const void* d_val) {
+  if (!plan) return 0;
+  SBLAS_ON_GPU(gpu);
+  return is_f64 ? sblas_plan_build_rowblocks_f64(nullptr, plan, d_colidx, (const double*)d_val, 0)
+                : sblas_plan_build_rowblocks_f32(nullptr, plan, d_colidx, (const float*)d_val, 0);
+}
 int sblas_scal_add_on(int gpu, int is_f64, void* d_v, double val, double beta, int64_t n) {
   SBLAS_ON_GPU(gpu);
   return is_f64 ? sblas_scal_add_f64(nullptr, (double*)d_v, val, beta, n)

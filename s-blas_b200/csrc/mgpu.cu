@@ -65,6 +65,32 @@ static int launch_finish(cudaStream_t st, const FinishList& fl, const T* carry, 
   return 0;
 }
 
+// ---- device-side barrier between the ranks of one node (one process per GPU) -------------------
+// Completes a peer-store stitched step without any host synchronisation: thread t of rank r
+// release-stores `epoch` into slot r of rank t's flag array (over NVLink), then spins (acquire,
+// system scope) until slot t of its own array reaches `epoch`.  The stores a rank's SpMV/SpMM
+// kernel made into the peers' replicas precede its flag store in stream order, so when the wait
+// returns every peer's rows have landed in the local replica.  Each rank owns one GPU, so the
+// spinning kernels of different ranks always run concurrently; the spin is bounded (about 2 s)
+// and reports a timeout through *status instead of hanging the device.
+__global__ void peer_barrier_kernel(int rank, int world, int32_t* local_flags, OutSpec<int32_t> peers,
+                                    int32_t epoch, int32_t* status) {
+  const int t = threadIdx.x;
+  if (t >= world) return;
+  if (t != rank) {
+    int32_t* dst = peers.ptr[t] + rank;
+    asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(dst), "r"(epoch) : "memory");
+    const long long t0 = clock64();
+    int32_t v;
+    do {
+      asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(local_flags + t) : "memory");
+      if (v - epoch >= 0) break;
+      __nanosleep(64);
+    } while (clock64() - t0 < 4000000000ll);
+    if (v - epoch < 0 && status) atomicExch(status, 1 + t);
+  }
+}
+
 // ---- logical GPU -> physical device ------------------------------------------------------------
 // SBLAS_DEVICE_MAP="0,0,1,1" runs a 4-way partition on two physical devices (several logical
 // GPUs may share one device: their kernels then simply run back to back on its default
@@ -306,6 +332,21 @@ int sblas_ipc_close(void* ptr) {
 }
 int sblas_ipc_free(void* ptr) {
   if (ptr) SBLAS_CUDA(cudaFree(ptr));
+  return 0;
+}
+
+int sblas_peer_barrier(void* stream, int rank, int world, int32_t* d_local_flags,
+                       void* const* d_peer_flags, int32_t epoch, int32_t* d_status) {
+  SBLAS_CHECK(world >= 1 && world <= SBLAS_MAX_GPU && rank >= 0 && rank < world, "peer_barrier: bad rank/world");
+  SBLAS_CHECK(d_local_flags && d_peer_flags, "peer_barrier: null flags");
+  if (world == 1) return 0;
+  OutSpec<int32_t> peers;
+  peers.n = world;
+  for (int i = 0; i < SBLAS_MAX_GPU - 1; ++i) peers.ptr[i] = nullptr;
+  SBLAS_CHECK(world <= SBLAS_MAX_GPU - 1, "peer_barrier: at most %d ranks", SBLAS_MAX_GPU - 1);
+  for (int i = 0; i < world; ++i) peers.ptr[i] = (int32_t*)d_peer_flags[i];
+  peer_barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(rank, world, d_local_flags, peers, epoch, d_status);
+  SBLAS_LAUNCH_CHECK();
   return 0;
 }
 

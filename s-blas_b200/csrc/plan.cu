@@ -177,6 +177,7 @@ int sblas_plan_destroy(sblasPlan_t p) {
   cudaSetDevice(p->device);
   for (TileTable& t : p->tables) { cudaFree(t.d_tile_row); if (t.d_tile_nnz) cudaFree(t.d_tile_nnz); }
   if (p->d_split_scratch) cudaFree(p->d_split_scratch);
+  rowblocks_free(p);
   cudaSetDevice(cur);
   delete p;
   return 0;

@@ -27,6 +27,20 @@ struct TileTable {
   int32_t max_tile_rows = 0;
 };
 
+// Row-block (R x 1 BCSR) mirror of A for SpMM, see spmm_rb.cu.  Only materialised when
+// fill = nnz / (n_blocks * R) >= kRowBlockMinFill.
+constexpr double kRowBlockMinFill = 0.5;
+struct RowBlocks {
+  int32_t R = 0;
+  int64_t n_blockrows = 0;
+  int64_t n_blocks = 0;          // 0: not materialised
+  double fill = 0.0;
+  bool is_f64 = true;
+  int32_t* d_ptr = nullptr;      // [n_blockrows + 1] first block of each block row
+  void* d_colmask = nullptr;     // int2 {col, presence mask} per block
+  void* d_val = nullptr;         // T[n_blocks * R], 0 where absent
+};
+
 }  // namespace sblas
 
 struct sblasPlan_st {
@@ -40,6 +54,7 @@ struct sblasPlan_st {
   // scratch for the split (carry) SpMV variant, grown on demand
   void* d_split_scratch = nullptr;
   size_t split_scratch_bytes = 0;
+  sblas::RowBlocks rb;
 };
 
 namespace sblas {
@@ -48,5 +63,6 @@ namespace sblas {
 int plan_get_table(sblasPlan_st* plan, cudaStream_t stream, int32_t row_weight, int32_t tile,
                    const TileTable** out);
 int plan_scratch(sblasPlan_st* plan, size_t bytes, void** out);
+void rowblocks_free(sblasPlan_st* plan);
 
 }  // namespace sblas

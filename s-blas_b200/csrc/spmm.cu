@@ -181,6 +181,104 @@ spmm_rm_kernel(const int32_t* __restrict__ tile_row, const int32_t* __restrict__
   }
 }
 
+// ---- ROWBLOCK (row-major B/C, R x 1 BCSR mirror of A, spmm_rb.cu) --------------------------------
+// One warp per block row (R adjacent rows); lane l owns columns (nb*32 + l)*VEC .. +VEC of the
+// panel for nb < NB.  Per block: one uniform (broadcast) load of {col, mask} and of the R values,
+// ONE gather of the B row slice, and up to R*NB vector multiply-adds from registers: the B slice
+// is reused R-fold.  U blocks are in flight per step.
+template <typename T, int VEC, int NB, int R, bool EXACT, int BLOCK>
+__global__ void __launch_bounds__(BLOCK)
+spmm_rb_kernel(int64_t n_blockrows, const int32_t* __restrict__ blk_ptr, const int2* __restrict__ colmask,
+               const T* __restrict__ bval, const T* __restrict__ B, int64_t ldb, MatSink<T> sink) {
+  using V = typename VecT<T, VEC>::type;
+  constexpr int U = NB >= 4 ? 1 : NB == 2 ? 2 : 4;
+  constexpr int WPB = BLOCK / 32;
+  const int lane = threadIdx.x & 31;
+  const int k = sink.k;
+  bool colok[NB];
+#pragma unroll
+  for (int nb = 0; nb < NB; ++nb) colok[nb] = (nb * 32 + lane) * VEC < k;
+  const T* bbase = B + lane * VEC;
+  for (int64_t br = (int64_t)blockIdx.x * WPB + (threadIdx.x >> 5); br < n_blockrows; br += (int64_t)gridDim.x * WPB) {
+    const int32_t b0 = blk_ptr[br], b1 = blk_ptr[br + 1];
+    V acc[R][NB];
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+#pragma unroll
+      for (int nb = 0; nb < NB; ++nb) vzero(acc[r][nb]);
+    for (int32_t b = b0; b < b1; b += U) {
+      int2 cm[U];
+      T vv[U][R];
+      V bv[U][NB];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        cm[u] = make_int2(0, 0);
+        if (b + u < b1) {
+          cm[u] = __ldg(colmask + b + u);
+#pragma unroll
+          for (int r = 0; r < R; ++r) vv[u][r] = __ldg(bval + (int64_t)(b + u) * R + r);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const T* brow = bbase + (int64_t)cm[u].x * ldb;
+#pragma unroll
+        for (int nb = 0; nb < NB; ++nb) {
+          vzero(bv[u][nb]);
+          if (cm[u].y != 0 && colok[nb]) bv[u][nb] = ldg_v(reinterpret_cast<const V*>(brow + nb * 32 * VEC));
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+          if (cm[u].y & (1 << r)) {
+#pragma unroll
+            for (int nb = 0; nb < NB; ++nb)
+              if (colok[nb]) vmac<EXACT>(vv[u][r], bv[u][nb], acc[r][nb]);
+          }
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const int64_t row = br * R + r;
+      if (row >= sink.rows) break;
+      const int slot = sink.partial_slot((int32_t)row);
+#pragma unroll
+      for (int nb = 0; nb < NB; ++nb) {
+        const int c0 = (nb * 32 + lane) * VEC;
+        if (c0 < k) {
+          if (slot >= 0) {
+            *reinterpret_cast<V*>(sink.carry + (int64_t)slot * sink.kpad + c0) = acc[r][nb];
+          } else {
+            const int64_t off = row * sink.ldc + c0;
+            const V cv = *reinterpret_cast<const V*>(sink.C + off);
+            const V res = vaxpby(sink.alpha, acc[r][nb], sink.beta, cv);
+            *reinterpret_cast<V*>(sink.C + off) = res;
+            for (int d = 0; d < sink.out.n; ++d) *reinterpret_cast<V*>(sink.out.ptr[d] + off) = res;
+          }
+        }
+      }
+    }
+  }
+}
+
+template <typename T, int VEC, bool EXACT>
+static int launch_rb(cudaStream_t st, const sblasPlan_st* plan, int NB, const T* B, int64_t ldb,
+                     const MatSink<T>& sink) {
+  const RowBlocks& rb = plan->rb;
+  constexpr int BLOCK = 256;
+  const int grid = (int)std::min<int64_t>(ceil_div(rb.n_blockrows, BLOCK / 32), (int64_t)kNumSM * 64);
+#define SBLAS_RB(NN)                                                                              \
+  spmm_rb_kernel<T, VEC, NN, 4, EXACT, BLOCK><<<grid, BLOCK, 0, st>>>(                             \
+      rb.n_blockrows, rb.d_ptr, (const int2*)rb.d_colmask, (const T*)rb.d_val, B, ldb, sink)
+  if (NB <= 1) SBLAS_RB(1);
+  else if (NB == 2) SBLAS_RB(2);
+  else SBLAS_RB(4);
+#undef SBLAS_RB
+  SBLAS_LAUNCH_CHECK();
+  return 0;
+}
+
 // ---- COLMAJOR ---------------------------------------------------------------------------------
 // Tile of A staged in shared memory once, then one pass per dense column: G lanes per row read
 // consecutive (col,val) pairs from shared memory (conflict-free), gather B[n*ldb + col] through
@@ -328,6 +426,31 @@ static int spmm_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
                (sink.carry == nullptr || aligned16(sink.carry));
     for (int d = 0; d < sink.out.n; ++d) vec = vec && aligned16(sink.out.ptr[d]);
     const int VEC = vec ? VF : 1;
+    // row-block mirror (R x 1 BCSR, built by sblas_plan_build_rowblocks_*): one B load feeds up to
+    // R adjacent rows.  Taken when the plan holds it for this value type, the operands are
+    // vectorisable and a row slice spans a whole warp (k >= 32*VEC); AUTO or SBLAS_SPMM_ROWBLOCK.
+    const int want = o ? o->variant : SBLAS_VARIANT_AUTO;
+    const bool rb_ok = vec && plan->rb.n_blocks > 0 && plan->rb.is_f64 == (sizeof(T) == 8) && k >= 32 * VF;
+    if (want == SBLAS_SPMM_ROWBLOCK && !rb_ok) {
+      set_error("spmm: SBLAS_SPMM_ROWBLOCK needs a plan with row blocks of this value type, 16-byte aligned operands and k >= %d", 32 * VF);
+      rc = 2;
+    }
+    if (rc == 0 && rb_ok && (want == SBLAS_VARIANT_AUTO || want == SBLAS_SPMM_ROWBLOCK)) {
+      const int rbpanel = 32 * VF * 4;
+      for (int32_t c_off = 0; c_off < k && rc == 0; c_off += rbpanel) {
+        const int kp = std::min<int32_t>(rbpanel, k - c_off);
+        const int NB = (kp + 32 * VF - 1) / (32 * VF);
+        MatSink<T> ps = sink;
+        ps.C = C + c_off;
+        ps.k = kp;
+        for (int d = 0; d < ps.out.n; ++d) ps.out.ptr[d] = sink.out.ptr[d] + c_off;
+        if (ps.carry) ps.carry = sink.carry + c_off;
+        rc = exact ? launch_rb<T, VF, true>(st, plan, NB, B + c_off, ldb, ps)
+                   : launch_rb<T, VF, false>(st, plan, NB, B + c_off, ldb, ps);
+      }
+      if (eph) { cudaStreamSynchronize(st); sblas_plan_destroy(eph); }
+      return rc;
+    }
     const int panel = 32 * VEC * 8;  // columns one launch covers at most
     for (int32_t c_off = 0; c_off < k && rc == 0; c_off += panel) {
       const int kp = std::min<int32_t>(panel, k - c_off);

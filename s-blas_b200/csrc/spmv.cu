@@ -248,17 +248,23 @@ struct PipeSink {
 // lanes -> consecutive elements: conflict-free for G > 1; for G = 1 the stride is the row
 // length), gather x with U independent loads in flight per lane, and accumulate in CSR order
 // with separately rounded mul/add (G = 1: bit-identical to spmv.h:24-30), then shuffle-reduce.
-template <typename T, int G, int U, int BLOCK, typename Sink>
+template <typename T, int G, int U, int BLOCK, bool CLAMP, typename Sink>
 __device__ __forceinline__ void consume_rows(const int32_t* __restrict__ s_col,
                                              const T* __restrict__ s_val,
                                              const int32_t* __restrict__ s_rp, int32_t nrows,
-                                             int32_t n0a, const T* __restrict__ x,
-                                             const Sink& sink) {
+                                             int32_t n0a, int32_t lo, int32_t hi,
+                                             const T* __restrict__ x, const Sink& sink) {
   const int gl = threadIdx.x & (G - 1), gi = threadIdx.x / G;
   for (int i0 = 0; i0 < nrows; i0 += BLOCK / G) {  // block-uniform trip count
     const int i = i0 + gi;
     const bool valid = i < nrows;
-    const int s = valid ? s_rp[i] - n0a : 0, e = valid ? s_rp[i + 1] - n0a : 0;
+    int s = valid ? s_rp[i] : 0, e = valid ? s_rp[i + 1] : 0;
+    if (CLAMP) {  // SPLIT tiles: rows are cut at the tile's nnz window [lo, hi)
+      s = min(max(s, lo), hi);
+      e = min(max(e, lo), hi);
+    }
+    s -= n0a;
+    e -= n0a;
     T sum = 0;
     for (int j0 = s + gl; j0 < e; j0 += G * U) {
       T vv[U], xx[U];
@@ -282,13 +288,80 @@ __device__ __forceinline__ void consume_rows(const int32_t* __restrict__ s_col,
   }
 }
 
-template <typename T, int BLOCK, int NSTAGE, int G>
+// A tile made of a few long row pieces (mean >= kPipeBlockModeAvg nnz): the whole CTA strides
+// over one row at a time, warp-shuffle + shared-memory reduction, one barrier per row.
+constexpr int kPipeBlockModeAvg = 128;
+template <typename T, int BLOCK, typename Sink>
+__device__ __forceinline__ void consume_rows_block(const int32_t* __restrict__ s_col,
+                                                   const T* __restrict__ s_val,
+                                                   const int32_t* __restrict__ s_rp, int32_t nrows,
+                                                   int32_t n0a, int32_t lo, int32_t hi,
+                                                   const T* __restrict__ x, const Sink& sink, T* red) {
+  constexpr int NW = BLOCK / 32;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  for (int i = 0; i < nrows; ++i) {
+    const int s = min(max(s_rp[i], lo), hi) - n0a, e = min(max(s_rp[i + 1], lo), hi) - n0a;
+    T sum = 0;
+    for (int j0 = s + tid; j0 < e; j0 += BLOCK * 4) {
+      T vv[4], xx[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int j = j0 + u * BLOCK;
+        if (j < e) { vv[u] = s_val[j]; xx[u] = __ldg(x + s_col[j]); }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (j0 + u * BLOCK < e) sum = add_rn(sum, mul_rn(vv[u], xx[u]));
+    }
+#pragma unroll
+    for (int m = 16; m > 0; m >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, m);
+    T* slot = red + (i & 1) * NW;  // two banks: one barrier per row is enough
+    if (lane == 0) slot[warp] = sum;
+    __syncthreads();
+    if (tid == 0) {
+      T tot = 0;
+#pragma unroll
+      for (int w = 0; w < NW; ++w) tot += slot[w];
+      sink.put(i, tot);
+    }
+  }
+}
+
+// SPLIT flavour of the sink: the piece of a row cut by the end of the tile goes to carry_out, the
+// last piece of a row begun in an earlier tile to head_val (folded by spmv_split_fixup_kernel)
+template <typename T>
+struct PipeSplitSink {
+  const RowSink<T>& sink;
+  const T* s_y;
+  int32_t ra, nfin;  // nfin = rows that END in this tile; local row nfin (if any) is cut
+  bool head_open;
+  T* carry_out;
+  T* head_val;
+  __device__ __forceinline__ void put(int i, T sum) const {
+    if (i == nfin) *carry_out = sum;
+    else if (i == 0 && head_open) *head_val = sum;
+    else sink.put_y(ra + i, sum, s_y[i]);
+  }
+};
+
+template <typename T>
+struct SplitArgs {  // only read by the SPLIT instantiation
+  int32_t T_items, rows;
+  int64_t nnz;
+  T* carry_out;
+  T* head_val;
+  int32_t* head_row;
+};
+
+template <typename T, int BLOCK, int NSTAGE, int G, bool SPLIT>
 __global__ void __launch_bounds__(BLOCK)
 spmv_pipe_kernel(const int32_t* __restrict__ tile_row, const int32_t* __restrict__ tile_nnz,
                  int32_t n_tiles, const int32_t* __restrict__ rowptr,
                  const int32_t* __restrict__ colidx, const T* __restrict__ val,
-                 const T* __restrict__ x, RowSink<T> sink, int32_t cap_nnz, int32_t cap_rows) {
+                 const T* __restrict__ x, RowSink<T> sink, int32_t cap_nnz, int32_t cap_rows,
+                 SplitArgs<T> sp) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
+  __shared__ T red[2 * (BLOCK / 32)];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw);     // [NSTAGE <= 8]
   int4* descs = reinterpret_cast<int4*>(smem_raw + 64);        // [NSTAGE] tile in each stage
   unsigned char* stages = smem_raw + kPipeHeaderBytes;
@@ -301,10 +374,19 @@ spmv_pipe_kernel(const int32_t* __restrict__ tile_row, const int32_t* __restrict
   __syncthreads();
   const int my_tiles = ((int)n_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
 
-  // descriptor of my i-th tile: (r0, r1, n0, n1)
+  // descriptor of my i-th tile: (r0, r1, n0, n1) = local rows [r0, r1), nnz window [n0, n1)
   auto load_desc = [&](int i) -> int4 {
     if (i >= my_tiles) return make_int4(0, 0, 0, 0);
     const int64_t b = (int64_t)blockIdx.x + (int64_t)i * gridDim.x;
+    if (SPLIT) {
+      // tile_row = merge-path split table (split_search_kernel): rows ra..rb-1 END in this tile,
+      // row rb (if < rows) is cut by its end; nnz window from the merge diagonal
+      const int32_t ra = __ldg(tile_row + b), rb = __ldg(tile_row + b + 1);
+      const int64_t da = b * sp.T_items;
+      const int64_t db = min(da + sp.T_items, (int64_t)sp.rows + sp.nnz);
+      const int cut = rb < sp.rows ? 1 : 0;  // .y = local row count | cut flag << 24 (SPLIT only)
+      return make_int4(ra, (rb - ra + cut) | (cut << 24), (int32_t)(da - ra), (int32_t)(db - rb));
+    }
     return make_int4(__ldg(tile_row + b), __ldg(tile_row + b + 1), __ldg(tile_nnz + b),
                      __ldg(tile_nnz + b + 1));
   };
@@ -314,7 +396,7 @@ spmv_pipe_kernel(const int32_t* __restrict__ tile_row, const int32_t* __restrict
     const int s = i % NSTAGE;
     uint64_t* bar = &bars[s];
     const PipeStage<T> st = pipe_stage<T>(stages, s, cap_nnz, cap_rows);
-    const int32_t r0 = d.x, nrows = d.y - d.x, n0 = d.z, n1 = d.w;
+    const int32_t r0 = d.x, nrows = SPLIT ? (d.y & 0xffffff) : d.y - d.x, n0 = d.z, n1 = d.w;
     const int32_t n0a = n0 & ~3;
     const int32_t m0 = min((n0 + 3) & ~3, n1);  // aligned middle [m0, m1)
     const int32_t m1 = max(n1 & ~3, m0);
@@ -359,11 +441,27 @@ spmv_pipe_kernel(const int32_t* __restrict__ tile_row, const int32_t* __restrict
     const PipeStage<T> st = pipe_stage<T>(stages, s, cap_nnz, cap_rows);
     mbar_wait(&bars[s], (uint32_t)(i / NSTAGE) & 1u);
     const int4 d = descs[s];
-    const int32_t r0 = d.x, nrows = d.y - d.x, n0 = d.z, n1 = d.w;
-    if (nrows > 0) {
+    const int32_t r0 = d.x, nrows = SPLIT ? (d.y & 0xffffff) : d.y - d.x, n0 = d.z, n1 = d.w;
+    if (SPLIT) {
+      const int64_t b = (int64_t)blockIdx.x + (int64_t)i * gridDim.x;
+      const bool has_cut = (d.y >> 24) != 0;
+      const int32_t nfin = nrows - (has_cut ? 1 : 0);               // rows r0 .. r0+nfin-1 end here
+      const bool head_open = nfin > 0 && st.rp[0] < n0;
+      if (tid == 0) {
+        sp.head_row[b] = head_open ? r0 : -1;
+        if (!has_cut) sp.carry_out[b] = T(0);
+      }
+      if (nrows > 0) {
+        const PipeSplitSink<T> ps{sink, st.y, r0, has_cut ? nfin : -1, head_open, sp.carry_out + b, sp.head_val + b};
+        if ((n1 - n0) >= kPipeBlockModeAvg * nrows)
+          consume_rows_block<T, BLOCK>(st.col, st.val, st.rp, nrows, n0 & ~3, n0, n1, x, ps, red);
+        else
+          consume_rows<T, G, 4, BLOCK, true>(st.col, st.val, st.rp, nrows, n0 & ~3, n0, n1, x, ps);
+      }
+    } else if (nrows > 0) {
       // rows straight from the staged tile: G lanes per row, U gathers in flight per lane
       const PipeSink<T> ps{sink, st.y, r0};
-      consume_rows<T, G, (G == 1 ? 8 : 4), BLOCK>(st.col, st.val, st.rp, nrows, n0 & ~3, x, ps);
+      consume_rows<T, G, (G == 1 ? 8 : 4), BLOCK, false>(st.col, st.val, st.rp, nrows, n0 & ~3, 0, 0, x, ps);
     }
     fence_proxy_async_smem();  // my generic-proxy accesses of this stage precede its next bulk fill
     __syncthreads();
@@ -501,9 +599,9 @@ static int pow2_lanes_pipe(double avg) {
   return avg <= 6 ? 1 : avg <= 12 ? 2 : avg <= 24 ? 4 : avg <= 48 ? 8 : avg <= 96 ? 16 : 32;
 }
 
-template <typename T>
+template <typename T, bool SPLIT>
 static const void* pipe_kernel_ptr(int stages, int G) {
-#define SBLAS_PK(NS, GG) (const void*)spmv_pipe_kernel<T, kSpmvBlock, NS, GG>
+#define SBLAS_PK(NS, GG) (const void*)spmv_pipe_kernel<T, kSpmvBlock, NS, GG, SPLIT>
 #define SBLAS_PKG(NS)                                                                          \
   (G <= 1 ? SBLAS_PK(NS, 1) : G == 2 ? SBLAS_PK(NS, 2) : G == 4 ? SBLAS_PK(NS, 4)               \
    : G == 8 ? SBLAS_PK(NS, 8) : G == 16 ? SBLAS_PK(NS, 16) : SBLAS_PK(NS, 32))
@@ -578,7 +676,7 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
         // lanes per row from the mean row length (one instantiation per launch keeps the
         // kernel small: ~50 registers instead of 160 with an in-kernel switch)
         int G = (o && o->lanes > 0) ? o->lanes : pow2_lanes_pipe(rows ? (double)(nnz / rows) : 0.0);  // integer mean, as the per-tile rule of TILE
-        const void* kern = pipe_kernel_ptr<T>(stages, G);
+        const void* kern = pipe_kernel_ptr<T, false>(stages, G);
         int per_sm = 0;
         if ((rc = set_smem_once<T>(kern, smem)) == 0) {
           cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kSpmvBlock, smem);
@@ -588,9 +686,10 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
           int n_sm = kNumSM;
           cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, plan->device);
           const int grid = std::min<int>(tt->n_tiles, n_sm * per_sm);
+          SplitArgs<T> sp{};
           void* args[] = {(void*)&tt->d_tile_row, (void*)&tt->d_tile_nnz, (void*)&tt->n_tiles, (void*)&rp,
                           (void*)&ci, (void*)&v, (void*)&x, (void*)&sink, (void*)&cap_nnz,
-                          (void*)&cap_rows};
+                          (void*)&cap_rows, (void*)&sp};
           cudaError_t e = cudaLaunchKernel(kern, dim3(grid), dim3(kSpmvBlock), args, smem, st);
           ++g_launches;
           if (e != cudaSuccess) { set_error("spmv pipe launch: %s", cudaGetErrorString(e)); rc = 3; }
@@ -643,17 +742,53 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
       T* carry_out = (T*)scratch;
       T* head_val = carry_out + tt->n_tiles;
       int32_t* head_row = (int32_t*)(head_val + tt->n_tiles);
-      const int32_t cap = (tile + 9) & ~3;
-      const int smem = cap * (int)sizeof(T) + (tile + 3) * (int)sizeof(int32_t);
-      auto kern = vec ? spmv_split_kernel<T, kSpmvBlock, true> : spmv_split_kernel<T, kSpmvBlock, false>;
-      if ((rc = set_smem_once<T>((const void*)kern, smem)) == 0) {
-        kern<<<tt->n_tiles, kSpmvBlock, smem, st>>>(tt->d_tile_row, tile, rows, nnz, rp, ci, v, x,
-                                                    sink, carry_out, head_val, head_row, cap);
+      if (vec) {
+        // staged (PIPE) flavour: same tiles, TMA bulk staging, persistent CTAs
+        const int32_t cap_nnz = (tile + 8 + 3) & ~3;
+        const int32_t cap_rows = tile + 2;
+        int stages = (o && o->stages > 0) ? std::min(std::max(o->stages, 2), 4) : 2;
+        auto smem_for = [&](int ns) { return (size_t)kPipeHeaderBytes + ns * pipe_stage_bytes<T>(cap_nnz, cap_rows); };
+        while (stages > 2 && smem_for(stages) > 110 * 1024) --stages;
+        const int smem = (int)smem_for(stages);
+        int G = (o && o->lanes > 0) ? o->lanes : pow2_lanes_pipe(rows ? (double)(nnz / std::max<int64_t>(rows - plan->empty_rows, 1)) : 0.0);
+        const void* kern = pipe_kernel_ptr<T, true>(stages, G);
+        int per_sm = 0;
+        if (smem > 200 * 1024) { set_error("spmv split: tile %d does not fit shared memory", tile); rc = 2; }
+        if (rc == 0 && (rc = set_smem_once<T>(kern, smem)) == 0) {
+          cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kSpmvBlock, smem);
+          if (e != cudaSuccess || per_sm < 1) { set_error("spmv split: occupancy query: %s", cudaGetErrorString(e)); rc = 1; }
+        }
+        if (rc == 0) {
+          int n_sm = kNumSM;
+          cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, plan->device);
+          const int grid = std::min<int>(tt->n_tiles, n_sm * per_sm);
+          SplitArgs<T> sp{tile, rows, nnz, carry_out, head_val, head_row};
+          const int32_t* no_nnz_table = nullptr;
+          void* args[] = {(void*)&tt->d_tile_row, (void*)&no_nnz_table, (void*)&tt->n_tiles, (void*)&rp,
+                          (void*)&ci, (void*)&v, (void*)&x, (void*)&sink, (void*)&cap_nnz,
+                          (void*)&cap_rows, (void*)&sp};
+          cudaError_t e = cudaLaunchKernel(kern, dim3(grid), dim3(kSpmvBlock), args, smem, st);
+          ++g_launches;
+          if (e != cudaSuccess) { set_error("spmv split(pipe) launch: %s", cudaGetErrorString(e)); rc = 3; }
+        }
+      } else {
+        const int32_t cap = (tile + 9) & ~3;
+        const int smem = cap * (int)sizeof(T) + (tile + 3) * (int)sizeof(int32_t);
+        auto kern = spmv_split_kernel<T, kSpmvBlock, false>;
+        if ((rc = set_smem_once<T>((const void*)kern, smem)) == 0) {
+          kern<<<tt->n_tiles, kSpmvBlock, smem, st>>>(tt->d_tile_row, tile, rows, nnz, rp, ci, v, x,
+                                                      sink, carry_out, head_val, head_row, cap);
+          ++g_launches;
+          cudaError_t e = cudaGetLastError();
+          if (e != cudaSuccess) { set_error("spmv split launch: %s", cudaGetErrorString(e)); rc = 3; }
+        }
+      }
+      if (rc == 0) {
         spmv_split_fixup_kernel<T><<<(int)ceil_div(tt->n_tiles, 256), 256, 0, st>>>(
             rp, tile, tt->n_tiles, carry_out, head_val, head_row, sink);
-        g_launches += 2;
+        ++g_launches;
         cudaError_t e = cudaGetLastError();
-        if (e != cudaSuccess) { set_error("spmv split launch: %s", cudaGetErrorString(e)); rc = 3; }
+        if (e != cudaSuccess) { set_error("spmv split fixup launch: %s", cudaGetErrorString(e)); rc = 3; }
       }
     }
   }

@@ -12,7 +12,8 @@ no reduction is needed).  x/B and y/C are replicated on every rank, as in the re
                  all-gathered in place (equal panels) or broadcast panel by panel;
   stitch="peer"  the replicas live in CUDA-IPC shared allocations; the kernel epilogue stores
                  each finished row into EVERY rank's replica over NVLink (sblasOpts.replica),
-                 so there is no separate collective — only a barrier.
+                 so there is no separate collective — only a device-side flag barrier
+                 (sblas_peer_barrier) enqueued behind the kernel, no host synchronisation.
 On CPU (gloo) the same host logic runs with a caller-supplied compute stand-in (tests only).
 """
 import ctypes as C
@@ -20,7 +21,7 @@ import ctypes as C
 import numpy as np
 
 from . import kernels as K
-from ._lib import ROW_MAJOR, check, lib, make_opts
+from ._lib import ROW_MAJOR, check, lib, make_opts, stream_ptr
 
 
 def _dist():
@@ -112,14 +113,26 @@ class RowSplitOp:
         self.rp, self.ci, self.val, self.k, self.ld = rp, ci, val, k, ld
         self.r0, self.r1 = self.row_begin[self.rank], self.row_begin[self.rank + 1]
         self.plan = plan if plan is not None else (K.Plan(rp, val.numel()) if self.r1 > self.r0 else None)
+        if plan is None and self.plan is not None and not (k == 1 and ld == 1):
+            self.plan.build_rowblocks(ci, val)      # SpMM: row-block mirror when it pays (sync2gpu work)
         self.stitch = stitch if self.world > 1 else "none"
         self.equal = len({self.row_begin[i + 1] - self.row_begin[i] for i in range(self.world)}) == 1
         self.opts = None
+        self.flags = None
         if self.stitch == "peer":
             esz = val.element_size()
             off = self.r0 * ld * esz
             reps = [p + off for r, p in enumerate(peer_ptrs) if r != self.rank]
             self.opts = make_opts(replicas=reps)
+            # flag words of the device-side barrier that completes the step (sblas_peer_barrier)
+            import torch
+            self.flags = IpcBuffer(256, val.device)
+            self.flag_ptrs = self.flags.open_peers()
+            self.flags.tensor(torch.float32, 64).zero_()
+            self.status = torch.zeros(1, dtype=torch.int32, device=val.device)
+            self.epoch = 0
+            torch.cuda.synchronize()
+            dist.barrier()          # everybody's flags are zero before the first signal
 
     def compute(self, xB, out, alpha, beta):
         """Local panel only (the part the roofline is quoted on)."""
@@ -139,9 +152,12 @@ class RowSplitOp:
         if self.stitch == "none":
             return
         if self.stitch == "peer":
-            import torch
-            torch.cuda.current_stream().synchronize()   # my stores have left
-            dist.barrier()                              # ... and so have everybody else's
+            # device-side: signal every peer, wait for every peer; no host synchronisation
+            self.epoch += 1
+            arr = (C.c_void_p * self.world)(*[C.c_void_p(p) for p in self.flag_ptrs])
+            check(lib().sblas_peer_barrier(stream_ptr(), C.c_int(self.rank), C.c_int(self.world),
+                                           C.c_void_p(self.flags.ptr.value), arr, C.c_int32(self.epoch),
+                                           C.c_void_p(self.status.data_ptr())), "peer_barrier")
             return
         if self.equal:
             dist.all_gather_into_tensor(out[:self.rows_total * self.ld],

@@ -101,6 +101,21 @@ class Plan:
                                               C.c_int64(self.nnz), vp(rowptr),
                                               C.byref(self.handle)), "plan_create")
 
+    def build_rowblocks(self, colidx, val, R=0, stream=None):
+        """Builds the R x 1 row-block mirror of A for SpMM (kept only when fill >= 0.5);
+        returns (R, n_blocks, fill).  colidx / val must stay alive as long as the plan."""
+        import torch
+        fn = getattr(lib(), "sblas_plan_build_rowblocks_" + _sfx(val.dtype))
+        with torch.cuda.device(val.device):
+            check(fn(stream_ptr(stream), self.handle, vp(colidx), vp(val), C.c_int32(R)), "plan_build_rowblocks")
+        return self.rowblock_stats()
+
+    def rowblock_stats(self):
+        R, nb, fill = C.c_int32(), C.c_int64(), C.c_double()
+        check(lib().sblas_plan_rowblock_stats(self.handle, C.byref(R), C.byref(nb), C.byref(fill)),
+              "plan_rowblock_stats")
+        return int(R.value), int(nb.value), float(fill.value)
+
     def stats(self):
         st = L.CsrStats()
         check(lib().sblas_plan_stats(self.handle, C.byref(st)), "plan_stats")

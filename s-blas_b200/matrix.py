@@ -85,6 +85,7 @@ class CsrSparseMatrix:
                 self.csrVal_gpu.append(_to_dev(self.csrVal, i))
                 with torch.cuda.device(physical(i)):
                     self.plans.append(K.Plan(self.csrRowPtr_gpu[i], self.nnz))
+                    self.plans[-1].build_rowblocks(self.csrColIdx_gpu[i], self.csrVal_gpu[i])
         else:
             p = K.csr_partition_nnz(self.csrRowPtr, n_gpu)
             self.avg_nnz = p["avg"]
@@ -99,6 +100,8 @@ class CsrSparseMatrix:
                 with torch.cuda.device(physical(i)):
                     self.plans.append(K.Plan(self.csrRowPtr_gpu[i], n_i) if n_i > 0 and
                                       len(p["rowptr"][i]) else None)
+                    if self.plans[-1] is not None:
+                        self.plans[-1].build_rowblocks(self.csrColIdx_gpu[i], self.csrVal_gpu[i])
                 if not quiet:                                               # matrix.h:388
                     print("gpu-%d,start-row:%d,stop-row:%d,num-rows:%d,num-nnz:%d" % (
                         i, self.starting_row_gpu[i], self.stoping_row_gpu[i],

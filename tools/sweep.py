@@ -59,6 +59,9 @@ def main():
     else:
         grid = [dict(tile=t, flags=f, lanes=l) for t in (256, 512, 1024, 2048, 4096, 16384) for f in (0, 1)
                 for l in ((0,) if args.grid == "default" else (0, 32))]
+    if wl['op'] == 'spmm':
+        print('rowblocks', plan.build_rowblocks(ci, v), flush=True)
+        grid = [dict(variant=pkg.SPMM_ROWBLOCK, flags=f) for f in (0, 1)] + [dict(variant=pkg.SPMM_ROWMAJOR, tile=t, flags=f) for t in (512, 2048) for f in (0, 1)]
     res = []
     if args.only is not None:
         grid = [g for g in grid if g.get('variant') == args.only]
