@@ -201,7 +201,7 @@ def run_ours(args, wl_key):
         ld = k
         xB = pkg.synth.fill_uniform(torch.empty(cols * ld, dtype=tdtype, device=dev), stream_id=11)
         yC = torch.ones(rows * ld, dtype=tdtype, device=dev)
-        opts = pkg.make_opts(variant=args.variant, tile=args.tile, lanes=args.lanes, flags=args.flags)
+        opts = pkg.make_opts(variant=args.variant, tile=args.tile, lanes=args.lanes, flags=args.flags, stages=args.stages)
 
         def step_compute():
             if op == "spmv":
@@ -366,6 +366,7 @@ def run_ours(args, wl_key):
     if rank == 0 and world == 1 and not args.no_cpu:
         cpu = cpu_baseline(wl_key, wl, op, f64, k, rp, ci, v, cols, budget_s=args.cpu_seconds)
 
+    traffic, traffic_src, kernel_name = ncu_traffic(wl_key, world, args)
     if rank == 0:
         out = {
             "metric": "CSR SpMV/SpMM GFLOP/s and % of HBM roofline at 1/2/4/8 B200 vs reference CPU",
@@ -386,12 +387,13 @@ def run_ours(args, wl_key):
                            **cfg_extra),
             "clocks": clocks, "gpu_launches": launches,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
+                         "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": int(abytes),
                          "kernel_ms_per_launch": tot_k_ms / args.steps,
                          "frac_of_nominal_8TBs": achieved / 8000.0,
                          "gather_model_bytes_per_launch": int(gather_bytes(op, loc_rows, cols, loc_nnz, loc_k, esz)),
-                         "kernel": "spmv_tile_kernel / spmm_rm_kernel (s-blas_b200/csrc)"},
+                         "kernel": kernel_name},
         }
         if e2e:
             out["e2e"] = e2e
@@ -401,6 +403,23 @@ def run_ours(args, wl_key):
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def ncu_traffic(wl_key, world, args):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the workload's dominant kernel, per launch,
+    from the committed `ncu --set full` capture (profiles/ncu_traffic.json: written from the
+    summaries beside it).  Only quoted for the default kernel choice on one GPU; else null."""
+    default = not (args.variant or args.tile or args.lanes or args.stages or args.flags) and args.scale_down == 1
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            ent = json.load(f).get(wl_key)
+    except (OSError, ValueError):
+        ent = None
+    if not ent:
+        return None, None, None
+    if world != 1 or not default:
+        return None, None, ent.get("kernel")
+    return ent.get("traffic_bytes"), ent.get("source"), ent.get("kernel")
 
 
 # ------------------------------------------------------------------------------- CPU arms ----
@@ -582,6 +601,7 @@ def main():
     ap.add_argument("--variant", type=int, default=0)
     ap.add_argument("--tile", type=int, default=0)
     ap.add_argument("--lanes", type=int, default=0)
+    ap.add_argument("--stages", type=int, default=0)
     ap.add_argument("--flags", type=int, default=0)
     ap.add_argument("--scale-down", type=int, default=1, help="shrink the workload (smoke runs)")
     ap.add_argument("--no-e2e", action="store_true")

@@ -54,9 +54,11 @@ enum {
                              tiles staged by TMA bulk copies + LDGSTS behind mbarriers (AUTO's choice) */
   SBLAS_SPMM_ROWMAJOR = 1, /* internal row-major B/C: one lane group per A row, 128-bit B gathers */
   SBLAS_SPMM_COLMAJOR = 2, /* native col-major B/C (the reference's host layout), no transposes */
-  SBLAS_SPMM_ROWBLOCK = 3  /* row-major B/C on the plan's R x 1 row-block mirror of A: one B load feeds
-                              up to R adjacent rows (structured inputs); AUTO takes it when the plan
-                              holds the mirror (sblas_plan_build_rowblocks_*) */
+  SBLAS_SPMM_ROWBLOCK = 3, /* row-major B/C on the plan's R x 1 row-block mirror of A: one B load feeds
+                              up to R adjacent rows (structured inputs); needs
+                              sblas_plan_build_rowblocks_* */
+  SBLAS_SPMM_ROWBLOCK_PIPE = 4 /* the same on persistent CTAs: mirror ranges and old C rows of the next
+                              tiles staged by TMA bulk copies behind mbarriers (AUTO's choice) */
 };
 enum {
   SBLAS_FLAG_FMA = 1,          /* allow fused multiply-add (default: separately rounded mul/add
@@ -65,7 +67,11 @@ enum {
   SBLAS_FLAG_HEAD_PARTIAL = 2, /* local row 0 continues a row begun on the previous GPU
                                   (matrix.h:443-445): its sum goes to carry[0..k), not to y/C */
   SBLAS_FLAG_TAIL_PARTIAL = 4, /* local last row continues on the next GPU: sum -> carry[k..2k) */
-  SBLAS_FLAG_NO_L1 = 8         /* gather x/B with L1::no_allocate */
+  SBLAS_FLAG_NO_L1 = 8,        /* gather x/B with L1::no_allocate */
+  SBLAS_FLAG_PREFETCH_B = 16,  /* SBLAS_SPMM_ROWBLOCK_PIPE: the producer warp prefetches the B rows of
+                                  the tile it just staged into L1; AUTO sets it for one-slice panels
+                                  (k <= 64 fp64 / 128 fp32), where it measured 5% faster */
+  SBLAS_FLAG_NO_PREFETCH_B = 32 /* ... never */
 };
 enum { SBLAS_ROW_MAJOR = 0, SBLAS_COL_MAJOR = 1 }; /* = MajorOrder, matrix.h:37 */
 

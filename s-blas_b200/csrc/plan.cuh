@@ -34,6 +34,9 @@ struct RowBlocks {
   int32_t R = 0;
   int64_t n_blockrows = 0;
   int64_t n_blocks = 0;          // 0: not materialised
+  int32_t max_tile_blocks = 0;   // most blocks in 8 consecutive block rows (tile of the pipelined kernel)
+  int32_t max_tile_blocks4 = 0;  // ... in 4 consecutive block rows (2 column slices per CTA)
+  int32_t max_tile_blocks2 = 0;  // ... in 2 consecutive block rows (4 column slices per CTA)
   double fill = 0.0;
   bool is_f64 = true;
   int32_t* d_ptr = nullptr;      // [n_blockrows + 1] first block of each block row

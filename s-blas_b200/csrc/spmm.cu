@@ -279,6 +279,321 @@ static int launch_rb(cudaStream_t st, const sblasPlan_st* plan, int NB, const T*
   return 0;
 }
 
+// ---- ROWBLOCK, pipelined (persistent CTAs, producer warp + 8 consumer warps) ---------------------
+// The kernel above is latency-bound: every warp walks blk_ptr -> {col,mask} -> B row -> old C as a
+// chain of dependent global loads, and its instruction stream carries ~70 warp instructions per
+// block for ~16 that are arithmetic.  Here a CTA walks CONSECUTIVE tiles of W block rows (so the
+// B rows a tile gathered are still in L1 for the next one: neighbouring rows of banded / stencil
+// inputs share most columns); warp 8 is a producer that keeps NSTAGE tiles of the A mirror in
+// flight — the tile's {col,mask} and value ranges are contiguous (cp.async.bulk, SASS UBLKCP), its
+// W+1 block pointers go by LDGSTS; one "full" mbarrier phase per stage collects all of it, one
+// "empty" mbarrier per stage hands the stage back (no CTA-wide barrier in the loop, warps drift
+// across stages).  Shared memory is kept small (2 x 12 KB stages + 16 KB) because what it takes
+// is taken from L1, and the L1 hit rate of the B gather is what the kernel lives on.
+// The 8 consumer warps are W x P: warp (w, p) owns block row w of the tile and column slice p
+// (NB*32*VEC columns) of the panel, so k up to P*NB*32*VEC is covered by ONE pass over A.  A
+// warp starts the copy of its R old C row slices (LDGSTS past L1, 16 bytes per lane) before the
+// block loop and reads them back in the epilogue.  The B gather is covered by U blocks in flight
+// per warp and 16-24 consumer warps per SM.  Instruction issue is the other bound, so the inner
+// loop is lean: shared loads by 32-bit shared address (LDS.64 {col,mask}, LDS.128 values), one
+// IMAD.WIDE for the B row address, unpredicated (column-clamped) LDG.128, a branch to an
+// unpredicated body when all U masks are full, one predicated pass for the < U blocks left at
+// the end of a block row: 24 instructions per block, 16 of them DMUL/DADD.
+// (Tried and dropped: a per-warp cp.async ring for the gathered B rows — LDGSTS + LDS doubled the
+// instruction count and the shared-memory wavefronts: 15.7 ms against 11.1 ms on the k=64 case;
+// cyclic tile distribution: 9.8 ms against 8.9 ms; C tiles staged by TMA: 32 KB less L1.)
+constexpr int kRbpConsumers = 8;                      // consumer warps per CTA
+constexpr int kRbpBlock = (kRbpConsumers + 1) * 32;   // + the producer warp
+constexpr int kRbpHeader = 128;                       // full[NSTAGE], empty[NSTAGE] barriers
+
+template <typename T, int R>
+__host__ __device__ inline size_t rbp_stage_bytes(int32_t cap_blocks) {
+  return (size_t)cap_blocks * 8 + (size_t)cap_blocks * R * sizeof(T) + 64;
+}
+// per consumer warp: the old C values of its R rows (16 bytes per lane, row and slice)
+template <int R>
+__host__ __device__ constexpr int rbp_cbuf_bytes(int NB) { return R * NB * 512; }
+
+// shared-memory loads by 32-bit shared address (volatile: never hoisted over the mbarrier waits)
+__device__ __forceinline__ int2 lds_i2(uint32_t a) {
+  int2 r;
+  asm volatile("ld.shared.v2.s32 {%0,%1}, [%2];" : "=r"(r.x), "=r"(r.y) : "r"(a));
+  return r;
+}
+__device__ __forceinline__ int lds_i1(uint32_t a) {
+  int r;
+  asm volatile("ld.shared.s32 %0, [%1];" : "=r"(r) : "r"(a));
+  return r;
+}
+template <int R>
+__device__ __forceinline__ void lds_vals(uint32_t a, double (&vv)[R]) {
+#pragma unroll
+  for (int r = 0; r < R; r += 2)
+    asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];" : "=d"(vv[r]), "=d"(vv[r + 1]) : "r"(a + r * 8));
+}
+template <int R>
+__device__ __forceinline__ void lds_vals(uint32_t a, float (&vv)[R]) {
+#pragma unroll
+  for (int r = 0; r < R; r += 4)
+    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(vv[r]), "=f"(vv[r + 1]), "=f"(vv[r + 2]), "=f"(vv[r + 3]) : "r"(a + r * 4));
+}
+__device__ __forceinline__ double2 lds_v(uint32_t a, double2) {
+  double2 r;
+  asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];" : "=d"(r.x), "=d"(r.y) : "r"(a));
+  return r;
+}
+__device__ __forceinline__ float4 lds_v(uint32_t a, float4) {
+  float4 r;
+  asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "r"(a));
+  return r;
+}
+
+// U blocks whose {col,mask} entries start at shared address a_cm and values at a_val (TAIL: only
+// the first n < U exist): gathers first, then the multiply-adds; a branch takes an unpredicated
+// body when all U masks are full.  bb[nb] = this lane's (clamped, always valid) column of slice nb
+// in row 0 of B: lanes past the panel edge compute garbage that the epilogue never stores.
+template <typename T, int VEC, int NB, int R, bool EXACT, int U, bool TAIL>
+__device__ __forceinline__ void rbp_blocks(uint32_t a_cm, uint32_t a_val, int n, const char* const (&bb)[NB],
+                                           uint32_t ldb_bytes, typename VecT<T, VEC>::type (&acc)[R][NB]) {
+  using V = typename VecT<T, VEC>::type;
+  constexpr int FULL = (1 << R) - 1;
+  int mask[U];
+  V bv[U][NB];
+  int allmask = FULL;
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    if (TAIL && u >= n) {
+      mask[u] = 0;
+    } else {
+      const int2 cm = lds_i2(a_cm + u * 8);
+      mask[u] = cm.y;
+      const uint64_t roff = (uint64_t)(uint32_t)cm.x * ldb_bytes;
+#pragma unroll
+      for (int nb = 0; nb < NB; ++nb) bv[u][nb] = ldg_v(reinterpret_cast<const V*>(bb[nb] + roff));
+    }
+    allmask &= mask[u];
+  }
+  if (!TAIL && allmask == FULL) {
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      T vv[R];
+      lds_vals<R>(a_val + u * (R * (int)sizeof(T)), vv);
+#pragma unroll
+      for (int r = 0; r < R; ++r)
+#pragma unroll
+        for (int nb = 0; nb < NB; ++nb) vmac<EXACT>(vv[r], bv[u][nb], acc[r][nb]);
+    }
+  } else {
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (mask[u] == 0) continue;
+      T vv[R];
+      lds_vals<R>(a_val + u * (R * (int)sizeof(T)), vv);
+#pragma unroll
+      for (int r = 0; r < R; ++r)
+        if (mask[u] & (1 << r)) {
+#pragma unroll
+          for (int nb = 0; nb < NB; ++nb) vmac<EXACT>(vv[r], bv[u][nb], acc[r][nb]);
+        }
+    }
+  }
+}
+
+template <typename T, int VEC, int NB, int R, bool EXACT, int NSTAGE>
+__global__ void __launch_bounds__(kRbpBlock, NB == 1 ? 3 : 2)
+spmm_rbp_kernel(int64_t n_blockrows, const int32_t* __restrict__ blk_ptr, const int2* __restrict__ colmask,
+                const T* __restrict__ bval, const T* __restrict__ B, uint32_t ldb_bytes, MatSink<T> sink,
+                int32_t cap_blocks, int32_t kp, int32_t logP, int32_t prefetch) {
+  using V = typename VecT<T, VEC>::type;
+  constexpr int U = NB == 1 ? 4 : 2;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw);
+  uint64_t* empty = full + NSTAGE;
+  unsigned char* stages = smem_raw + kRbpHeader;
+  const int W = kRbpConsumers >> logP;  // block rows per tile
+  const size_t stage_bytes = rbp_stage_bytes<T, R>(cap_blocks);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < NSTAGE; ++s) {
+      mbar_init(&full[s], 32 + 1);             // producer lanes' LDGSTS groups + the expect_tx arrive
+      mbar_init(&empty[s], kRbpConsumers);     // one arrive per consumer warp
+    }
+    mbar_fence_init();
+  }
+  __syncthreads();
+  const int64_t n_tiles = (n_blockrows + W - 1) / W;
+  // consecutive tiles per CTA: neighbouring block rows share most of their columns (banded /
+  // stencil inputs), so the B rows of tile i are still in L1 when tile i+1 gathers them
+  const int64_t per_cta = (n_tiles + gridDim.x - 1) / gridDim.x;
+  const int64_t tile0 = (int64_t)blockIdx.x * per_cta;
+  const int my_tiles = (int)max((int64_t)0, min(per_cta, n_tiles - tile0));
+
+  auto stage_ptrs = [&](int s, int2*& s_cm, T*& s_val, int32_t*& s_ptr) {
+    unsigned char* p = stages + (size_t)s * stage_bytes;
+    s_cm = reinterpret_cast<int2*>(p);
+    p += (size_t)cap_blocks * 8;
+    s_val = reinterpret_cast<T*>(p);
+    p += (size_t)cap_blocks * R * sizeof(T);
+    s_ptr = reinterpret_cast<int32_t*>(p);
+  };
+
+  if (warp == kRbpConsumers) {
+    // ---- producer warp --------------------------------------------------------------------------
+#pragma unroll 1
+    for (int i = 0; i < my_tiles; ++i) {
+      const int s = i % NSTAGE;
+      const int64_t br0 = (tile0 + i) * W;
+      const int32_t nbr = (int32_t)min((int64_t)W, n_blockrows - br0);
+      const int32_t p0 = __ldg(blk_ptr + br0), p1 = __ldg(blk_ptr + br0 + nbr);
+      if (i >= NSTAGE) mbar_wait(&empty[s], (uint32_t)(i / NSTAGE - 1) & 1u);
+      int2* s_cm; T* s_val; int32_t* s_ptr;
+      stage_ptrs(s, s_cm, s_val, s_ptr);
+      const int32_t p0a = p0 & ~1;                 // {col,mask} entries are 8 bytes: bulk needs pairs
+      const int32_t m0 = min((p0 + 1) & ~1, p1);   // aligned middle [m0, m1)
+      const int32_t m1 = max(p1 & ~1, m0);
+      if (lane == 0) {
+        const uint32_t nb = (uint32_t)(p1 - p0);
+        const uint32_t bytes = (uint32_t)(m1 - m0) * 8u + nb * (uint32_t)(R * sizeof(T));
+        mbar_arrive_expect_tx(&full[s], bytes);
+        if (m1 > m0) bulk_g2s(s_cm + (m0 - p0a), colmask + m0, (uint32_t)(m1 - m0) * 8u, &full[s]);
+        if (nb) bulk_g2s(s_val + (size_t)(p0 - p0a) * R, bval + (size_t)p0 * R, nb * (uint32_t)(R * sizeof(T)), &full[s]);
+      }
+      if (lane == 0 && m0 > p0) cp_async8(s_cm + (p0 - p0a), colmask + p0);   // head (1 entry)
+      if (lane == 1 && p1 > m1) cp_async8(s_cm + (m1 - p0a), colmask + m1);   // tail (1 entry)
+      if (lane >= 2 && lane < 2 + nbr + 1) cp_async4(s_ptr + (lane - 2), blk_ptr + br0 + (lane - 2));
+      cp_async_mbar_arrive_noinc(&full[s]);
+      if (prefetch) {
+        // the B rows this tile will gather: pull them into L1 while the consumers are still on
+        // the previous tile (first touches come from HBM, nobody else prefetches them).
+        // (cp.async.bulk.prefetch.L2 per row instead: 12.5 ms against 9.3 ms without, TMA-bound.)
+        mbar_wait(&full[s], (uint32_t)(i / NSTAGE) & 1u);
+        const uint32_t rowb = (uint32_t)kp * (uint32_t)sizeof(T);
+        for (int32_t j = (p0 - p0a) + lane; j < p1 - p0a; j += 32) {
+          const char* brow = reinterpret_cast<const char*>(B) + (uint64_t)(uint32_t)s_cm[j].x * ldb_bytes;
+          for (uint32_t o = 0; o < rowb; o += 128) prefetch_l1(brow + o);
+        }
+      }
+    }
+    return;
+  }
+
+  // ---- consumer warps: (w, p) = (block row of the tile, column slice of the panel) ---------------
+  const int w = warp >> logP, p = warp & ((1 << logP) - 1);
+  const int cbase = (p * NB * 32 + lane) * VEC;  // first column of this lane, slice nb adds nb*32*VEC
+  bool colok[NB];
+  const char* bb[NB];
+#pragma unroll
+  for (int nb = 0; nb < NB; ++nb) {
+    const int c0 = cbase + nb * 32 * VEC;
+    colok[nb] = c0 < kp;
+    bb[nb] = reinterpret_cast<const char*>(B + min(c0, kp - VEC));   // clamped: loads stay unpredicated
+  }
+  const uint32_t stages_a = smem_u32(stages);
+  const uint32_t off_val = (uint32_t)cap_blocks * 8u, off_ptr = off_val + (uint32_t)cap_blocks * (uint32_t)(R * sizeof(T));
+  // this warp's C buffer, behind the stages: lane l keeps the 16 bytes it copied at (r*NB+nb)*512 + l*16
+  const uint32_t a_C = stages_a + (uint32_t)(NSTAGE * stage_bytes) + (uint32_t)(warp * rbp_cbuf_bytes<R>(NB) + lane * 16);
+
+#pragma unroll 1
+  for (int i = 0; i < my_tiles; ++i) {
+    const int s = i % NSTAGE;
+    const uint32_t st_a = stages_a + (uint32_t)s * (uint32_t)stage_bytes;
+    mbar_wait(&full[s], (uint32_t)(i / NSTAGE) & 1u);
+    const int64_t br = (tile0 + i) * W + w;
+    if (br < n_blockrows) {
+      const int32_t p0a = lds_i1(st_a + off_ptr) & ~1;
+      const int2 bp = make_int2(lds_i1(st_a + off_ptr + w * 4), lds_i1(st_a + off_ptr + w * 4 + 4));
+      // old C values of my R rows: LDGSTS past L1 now, read back in the epilogue
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        const int64_t row = br * R + r;
+        if (row < sink.rows) {
+#pragma unroll
+          for (int nb = 0; nb < NB; ++nb)
+            if (colok[nb]) cp_async16_cg(a_C + (uint32_t)((r * NB + nb) * 512), sink.C + row * sink.ldc + cbase + nb * 32 * VEC);
+        }
+      }
+      cp_async_commit();
+      V acc[R][NB];
+#pragma unroll
+      for (int r = 0; r < R; ++r)
+#pragma unroll
+        for (int nb = 0; nb < NB; ++nb) vzero(acc[r][nb]);
+      uint32_t a_cm = st_a + (uint32_t)(bp.x - p0a) * 8u;
+      uint32_t a_val = st_a + off_val + (uint32_t)(bp.x - p0a) * (uint32_t)(R * sizeof(T));
+      const uint32_t a_end = st_a + (uint32_t)(bp.y - p0a) * 8u;
+#pragma unroll 1
+      for (; a_cm + U * 8 <= a_end; a_cm += U * 8, a_val += U * R * sizeof(T))
+        rbp_blocks<T, VEC, NB, R, EXACT, U, false>(a_cm, a_val, U, bb, ldb_bytes, acc);
+      if (a_cm < a_end)
+        rbp_blocks<T, VEC, NB, R, EXACT, U, true>(a_cm, a_val, (int)(a_end - a_cm) >> 3, bb, ldb_bytes, acc);
+      cp_async_wait<0>();
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        const int64_t row = br * R + r;
+        if (row >= sink.rows) break;
+        const int slot = sink.partial_slot((int32_t)row);
+#pragma unroll
+        for (int nb = 0; nb < NB; ++nb) {
+          const int c0 = cbase + nb * 32 * VEC;
+          if (colok[nb]) {
+            if (slot >= 0) {
+              *reinterpret_cast<V*>(sink.carry + (int64_t)slot * sink.kpad + c0) = acc[r][nb];
+            } else {
+              const int64_t off = row * sink.ldc + c0;
+              const V cv = lds_v(a_C + (uint32_t)((r * NB + nb) * 512), V());
+              const V res = vaxpby(sink.alpha, acc[r][nb], sink.beta, cv);
+              *reinterpret_cast<V*>(sink.C + off) = res;
+              for (int d = 0; d < sink.out.n; ++d) *reinterpret_cast<V*>(sink.out.ptr[d] + off) = res;
+            }
+          }
+        }
+      }
+    }
+    fence_proxy_async_smem();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&empty[s]);
+  }
+}
+
+// P = column slices per CTA (1, 2, 4); panel = P*NB*32*VEC columns per pass over A
+template <typename T, int VEC, bool EXACT>
+static int launch_rbp(cudaStream_t st, const sblasPlan_st* plan, int NB, int logP, int stages, const T* B,
+                      int64_t ldb, const MatSink<T>& sink, int32_t kp) {
+  const RowBlocks& rb = plan->rb;
+  constexpr int R = 4;
+  const int W = kRbpConsumers >> logP;
+  const int32_t tile_blocks = logP == 0 ? rb.max_tile_blocks : logP == 1 ? rb.max_tile_blocks4 : rb.max_tile_blocks2;
+  const int32_t cap_blocks = (tile_blocks + 2 + 1) & ~1;
+  const void* kern;
+  if (stages <= 2) kern = NB <= 1 ? (const void*)spmm_rbp_kernel<T, VEC, 1, R, EXACT, 2>
+                                  : (const void*)spmm_rbp_kernel<T, VEC, 2, R, EXACT, 2>;
+  else kern = NB <= 1 ? (const void*)spmm_rbp_kernel<T, VEC, 1, R, EXACT, 3>
+                      : (const void*)spmm_rbp_kernel<T, VEC, 2, R, EXACT, 3>;
+  const int ns = stages <= 2 ? 2 : 3;
+  const size_t smem = kRbpHeader + ns * rbp_stage_bytes<T, R>(cap_blocks) + (size_t)kRbpConsumers * rbp_cbuf_bytes<R>(NB <= 1 ? 1 : 2);
+  SBLAS_CHECK(smem <= 200 * 1024, "spmm rowblock pipe: tile needs %zu bytes of shared memory", smem);
+  if (smem > 48 * 1024) SBLAS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int per_sm = 0;
+  SBLAS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kRbpBlock, smem));
+  SBLAS_CHECK(per_sm >= 1, "spmm rowblock pipe: kernel does not fit an SM");
+  int n_sm = kNumSM;
+  cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, plan->device);
+  const int64_t n_tiles = ceil_div(rb.n_blockrows, W);
+  const int grid = (int)std::min<int64_t>(n_tiles, (int64_t)n_sm * per_sm);
+  const int2* cm = (const int2*)rb.d_colmask;
+  const T* bv = (const T*)rb.d_val;
+  const uint32_t ldb_bytes = (uint32_t)(ldb * (int64_t)sizeof(T));
+  const int32_t prefetch = (sink.flags & SBLAS_FLAG_NO_PREFETCH_B) ? 0
+                           : ((sink.flags & SBLAS_FLAG_PREFETCH_B) || (NB <= 1 && logP == 0)) ? 1 : 0;
+  void* args[] = {(void*)&rb.n_blockrows, (void*)&rb.d_ptr, (void*)&cm, (void*)&bv, (void*)&B, (void*)&ldb_bytes,
+                  (void*)&sink, (void*)&cap_blocks, (void*)&kp, (void*)&logP, (void*)&prefetch};
+  SBLAS_CUDA(cudaLaunchKernel(kern, dim3(grid), dim3(kRbpBlock), args, smem, st));
+  ++g_launches;
+  return 0;
+}
+
 // ---- COLMAJOR ---------------------------------------------------------------------------------
 // Tile of A staged in shared memory once, then one pass per dense column: G lanes per row read
 // consecutive (col,val) pairs from shared memory (conflict-free), gather B[n*ldb + col] through
@@ -326,7 +641,7 @@ spmm_cm_kernel(const int32_t* __restrict__ tile_row, const int32_t* __restrict__
                const int32_t* __restrict__ colidx, const T* __restrict__ val,
                const T* __restrict__ B, int64_t ldb, MatSink<T> sink, int32_t cap_nnz,
                int32_t force_lanes) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
+  extern __shared__ __align__(128) unsigned char smem_raw[];
   T* s_val = reinterpret_cast<T*>(smem_raw);
   int32_t* s_col = reinterpret_cast<int32_t*>(s_val + cap_nnz);
   int32_t* s_rp = s_col + cap_nnz;
@@ -431,12 +746,28 @@ static int spmm_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
     // vectorisable and a row slice spans a whole warp (k >= 32*VEC); AUTO or SBLAS_SPMM_ROWBLOCK.
     const int want = o ? o->variant : SBLAS_VARIANT_AUTO;
     const bool rb_ok = vec && plan->rb.n_blocks > 0 && plan->rb.is_f64 == (sizeof(T) == 8) && k >= 32 * VF;
-    if (want == SBLAS_SPMM_ROWBLOCK && !rb_ok) {
+    if ((want == SBLAS_SPMM_ROWBLOCK || want == SBLAS_SPMM_ROWBLOCK_PIPE) && !rb_ok) {
       set_error("spmm: SBLAS_SPMM_ROWBLOCK needs a plan with row blocks of this value type, 16-byte aligned operands and k >= %d", 32 * VF);
       rc = 2;
     }
-    if (rc == 0 && rb_ok && (want == SBLAS_VARIANT_AUTO || want == SBLAS_SPMM_ROWBLOCK)) {
-      const int rbpanel = 32 * VF * 4;
+    if (rc == 0 && rb_ok && (want == SBLAS_VARIANT_AUTO || want == SBLAS_SPMM_ROWBLOCK || want == SBLAS_SPMM_ROWBLOCK_PIPE)) {
+      // pipelined flavour: needs the tile statistics and a B pitch below 4 GB.  One pass over A
+      // covers P*NB slices of 32*VF columns: (NB, P) = (1,1) (2,1) (2,2) for 1, 2, 3-4 slices;
+      // opts->lanes = 1/2/4 forces P.  AUTO takes it; SBLAS_SPMM_ROWBLOCK keeps the unpiped kernel.
+      const bool piped = want != SBLAS_SPMM_ROWBLOCK && plan->rb.max_tile_blocks > 0 &&
+                         ldb * (int64_t)sizeof(T) < (1ll << 32);
+      const int slice = 32 * VF;
+      int NBp = 1, logP = 0;
+      if (piped) {
+        const int n_slices = (k + slice - 1) / slice;
+        if (n_slices >= 3) { NBp = 2; logP = 1; }
+        else if (n_slices == 2) { NBp = 2; logP = 0; }
+        if (o && (o->lanes == 1 || o->lanes == 2 || o->lanes == 4)) {
+          logP = o->lanes == 1 ? 0 : o->lanes == 2 ? 1 : 2;
+          NBp = n_slices > (1 << logP) ? 2 : 1;
+        }
+      }
+      const int rbpanel = piped ? slice * NBp * (1 << logP) : slice * 4;
       for (int32_t c_off = 0; c_off < k && rc == 0; c_off += rbpanel) {
         const int kp = std::min<int32_t>(rbpanel, k - c_off);
         const int NB = (kp + 32 * VF - 1) / (32 * VF);
@@ -445,8 +776,12 @@ static int spmm_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
         ps.k = kp;
         for (int d = 0; d < ps.out.n; ++d) ps.out.ptr[d] = sink.out.ptr[d] + c_off;
         if (ps.carry) ps.carry = sink.carry + c_off;
-        rc = exact ? launch_rb<T, VF, true>(st, plan, NB, B + c_off, ldb, ps)
-                   : launch_rb<T, VF, false>(st, plan, NB, B + c_off, ldb, ps);
+        if (piped && kp % VF == 0)
+          rc = exact ? launch_rbp<T, VF, true>(st, plan, NBp, logP, o ? o->stages : 0, B + c_off, ldb, ps, kp)
+                     : launch_rbp<T, VF, false>(st, plan, NBp, logP, o ? o->stages : 0, B + c_off, ldb, ps, kp);
+        else
+          rc = exact ? launch_rb<T, VF, true>(st, plan, std::min(NB, 4), B + c_off, ldb, ps)
+                     : launch_rb<T, VF, false>(st, plan, std::min(NB, 4), B + c_off, ldb, ps);
       }
       if (eph) { cudaStreamSynchronize(st); sblas_plan_destroy(eph); }
       return rc;

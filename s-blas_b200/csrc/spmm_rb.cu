@@ -63,12 +63,22 @@ rb_merge_kernel(int32_t rows, const int32_t* __restrict__ rowptr, const int32_t*
   if (!FILL) counts[br] = n;
 }
 
+// most blocks in W consecutive block rows (staging capacity of the pipelined kernel)
+__global__ void rb_tile_max_kernel(const int32_t* __restrict__ blk_ptr, int64_t n_blockrows, int W, int32_t* out) {
+  const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  const int64_t n_tiles = (n_blockrows + W - 1) / W;
+  int32_t v = 0;
+  if (t < n_tiles) v = blk_ptr[min((t + 1) * W, n_blockrows)] - blk_ptr[t * W];
+  v = warp_max(v);
+  if ((threadIdx.x & 31) == 0) atomicMax(out, v);
+}
+
 template <typename T, int R>
 static int build_rowblocks(cudaStream_t st, sblasPlan_st* plan, const int32_t* ci, const T* val, bool force) {
   const int64_t nbr = ((int64_t)plan->rows + R - 1) / R;
   RowBlocks& rb = plan->rb;
   int32_t* counts = nullptr;
-  SBLAS_CUDA(cudaMalloc(&counts, sizeof(int32_t) * (size_t)(nbr + 1)));
+  SBLAS_CUDA(cudaMalloc(&counts, sizeof(int32_t) * (size_t)(nbr + 4)));  // >= 3 slots for the tile statistics
   SBLAS_CUDA(cudaMemsetAsync(counts, 0, sizeof(int32_t) * (size_t)(nbr + 1), st));
   const int grid = (int)ceil_div(nbr, 128);
   rb_merge_kernel<R, false, T><<<grid, 128, 0, st>>>(plan->rows, plan->d_rowptr, ci, val, counts, nullptr, nullptr, nullptr);
@@ -100,7 +110,20 @@ static int build_rowblocks(cudaStream_t st, sblasPlan_st* plan, const int32_t* c
   rb_merge_kernel<R, true, T><<<grid, 128, 0, st>>>(plan->rows, plan->d_rowptr, ci, val, counts, rb.d_ptr,
                                                     (int2*)rb.d_colmask, (T*)rb.d_val);
   SBLAS_LAUNCH_CHECK();
+  // counts[0..2] are free again: reuse them for the tile statistics (W = 8, 4, 2 block rows)
+  SBLAS_CUDA(cudaMemsetAsync(counts, 0, 3 * sizeof(int32_t), st));
+  int32_t tile_max[3] = {0, 0, 0};
+  for (int j = 0; j < 3; ++j) {
+    const int W = 8 >> j;
+    const int64_t n_tiles = ceil_div(nbr, W);
+    rb_tile_max_kernel<<<(int)ceil_div(n_tiles, 256), 256, 0, st>>>(rb.d_ptr, nbr, W, counts + j);
+    SBLAS_LAUNCH_CHECK();
+  }
+  SBLAS_CUDA(cudaMemcpyAsync(tile_max, counts, 3 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
   SBLAS_CUDA(cudaStreamSynchronize(st));
+  rb.max_tile_blocks = tile_max[0];
+  rb.max_tile_blocks4 = tile_max[1];
+  rb.max_tile_blocks2 = tile_max[2];
   SBLAS_CUDA(cudaFree(counts));
   return 0;
 }

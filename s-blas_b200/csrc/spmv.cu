@@ -112,6 +112,42 @@ __device__ __forceinline__ void reduce_rows_dispatch(int lanes, const T* s_prod,
   }
 }
 
+// Same, for SPLIT tiles: row pointers are clamped to the tile's nnz window [lo, hi).
+template <typename T, int G, int BLOCK, typename Sink>
+__device__ __forceinline__ void reduce_rows_clamped(const T* s_prod, const int32_t* s_rp, int32_t nrows,
+                                                    int32_t n0a, int32_t lo, int32_t hi, const Sink& sink) {
+  const int tid = threadIdx.x;
+  const int gl = tid & (G - 1), gi = tid / G;
+  for (int i0 = 0; i0 < nrows; i0 += BLOCK / G) {  // block-uniform trip count
+    const int i = i0 + gi;
+    const bool valid = i < nrows;
+    const int s = valid ? min(max(s_rp[i], lo), hi) - n0a : 0;
+    const int e = valid ? min(max(s_rp[i + 1], lo), hi) - n0a : 0;
+    T sum = 0;
+    if (G == 1) {
+      for (int j = s; j < e; ++j) sum = add_rn(sum, s_prod[j]);
+    } else {
+      for (int j = s + gl; j < e; j += G) sum += s_prod[j];
+#pragma unroll
+      for (int m = G / 2; m > 0; m >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, m);
+    }
+    if (valid && gl == 0) sink.put(i, sum);
+  }
+}
+template <typename T, int BLOCK, typename Sink>
+__device__ __forceinline__ void reduce_rows_clamped_dispatch(int lanes, const T* s_prod, const int32_t* s_rp,
+                                                             int32_t nrows, int32_t n0a, int32_t lo, int32_t hi,
+                                                             const Sink& sink) {
+  switch (lanes) {
+    case 1: reduce_rows_clamped<T, 1, BLOCK>(s_prod, s_rp, nrows, n0a, lo, hi, sink); break;
+    case 2: reduce_rows_clamped<T, 2, BLOCK>(s_prod, s_rp, nrows, n0a, lo, hi, sink); break;
+    case 4: reduce_rows_clamped<T, 4, BLOCK>(s_prod, s_rp, nrows, n0a, lo, hi, sink); break;
+    case 8: reduce_rows_clamped<T, 8, BLOCK>(s_prod, s_rp, nrows, n0a, lo, hi, sink); break;
+    case 16: reduce_rows_clamped<T, 16, BLOCK>(s_prod, s_rp, nrows, n0a, lo, hi, sink); break;
+    default: reduce_rows_clamped<T, 32, BLOCK>(s_prod, s_rp, nrows, n0a, lo, hi, sink); break;
+  }
+}
+
 __device__ __forceinline__ int lanes_for_avg(int avg) {
   return avg <= 6 ? 1 : avg <= 12 ? 2 : avg <= 24 ? 4 : avg <= 48 ? 8 : avg <= 96 ? 16 : 32;
 }
@@ -452,11 +488,23 @@ spmv_pipe_kernel(const int32_t* __restrict__ tile_row, const int32_t* __restrict
         if (!has_cut) sp.carry_out[b] = T(0);
       }
       if (nrows > 0) {
+        // skewed rows: balance the x gathers first (every thread takes the same number of nnz,
+        // products overwrite the staged values), then reduce the rows from shared memory
+        const int32_t n0a = n0 & ~3;
+        for (int j = (n0 - n0a) + tid; j < n1 - n0a; j += BLOCK * 4) {
+          T vv[4], xx[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const int jj = j + u * BLOCK;
+            if (jj < n1 - n0a) { vv[u] = st.val[jj]; xx[u] = __ldg(x + st.col[jj]); }
+          }
+#pragma unroll
+          for (int u = 0; u < 4; ++u)
+            if (j + u * BLOCK < n1 - n0a) st.val[j + u * BLOCK] = mul_rn(vv[u], xx[u]);
+        }
+        __syncthreads();
         const PipeSplitSink<T> ps{sink, st.y, r0, has_cut ? nfin : -1, head_open, sp.carry_out + b, sp.head_val + b};
-        if ((n1 - n0) >= kPipeBlockModeAvg * nrows)
-          consume_rows_block<T, BLOCK>(st.col, st.val, st.rp, nrows, n0 & ~3, n0, n1, x, ps, red);
-        else
-          consume_rows<T, G, 4, BLOCK, true>(st.col, st.val, st.rp, nrows, n0 & ~3, n0, n1, x, ps);
+        reduce_rows_clamped_dispatch<T, BLOCK>(lanes_for_avg((n1 - n0) / nrows), st.val, st.rp, nrows, n0a, n0, n1, ps);
       }
     } else if (nrows > 0) {
       // rows straight from the staged tile: G lanes per row, U gathers in flight per lane
@@ -742,8 +790,10 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
       T* carry_out = (T*)scratch;
       T* head_val = carry_out + tt->n_tiles;
       int32_t* head_row = (int32_t*)(head_val + tt->n_tiles);
-      if (vec) {
-        // staged (PIPE) flavour: same tiles, TMA bulk staging, persistent CTAs
+      if (vec && o && o->stages > 0) {
+        // staged (PIPE) flavour, on request (opts->stages): same tiles, TMA bulk staging, persistent
+        // CTAs.  Measured slower than the one-tile-per-CTA kernel below on power-law inputs
+        // (config 4: 0.94 ms against 0.66 ms), so AUTO does not take it.
         const int32_t cap_nnz = (tile + 8 + 3) & ~3;
         const int32_t cap_rows = tile + 2;
         int stages = (o && o->stages > 0) ? std::min(std::max(o->stages, 2), 4) : 2;
@@ -774,7 +824,7 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
       } else {
         const int32_t cap = (tile + 9) & ~3;
         const int smem = cap * (int)sizeof(T) + (tile + 3) * (int)sizeof(int32_t);
-        auto kern = spmv_split_kernel<T, kSpmvBlock, false>;
+        auto kern = vec ? spmv_split_kernel<T, kSpmvBlock, true> : spmv_split_kernel<T, kSpmvBlock, false>;
         if ((rc = set_smem_once<T>((const void*)kern, smem)) == 0) {
           kern<<<tt->n_tiles, kSpmvBlock, smem, st>>>(tt->d_tile_row, tile, rows, nnz, rp, ci, v, x,
                                                       sink, carry_out, head_val, head_row, cap);

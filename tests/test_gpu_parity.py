@@ -59,7 +59,7 @@ MATS = {
 
 @pytest.mark.parametrize("dtype", [np.float64, np.float32])
 @pytest.mark.parametrize("mat", list(MATS))
-@pytest.mark.parametrize("variant", ["auto", "tile", "pipe", "pipe2", "vector", "split", "noplan"])
+@pytest.mark.parametrize("variant", ["auto", "tile", "pipe", "pipe2", "vector", "split", "splitp", "noplan"])
 def test_spmv_vs_oracle(sblas, dev, oracle, dtype, mat, variant):
     import torch
     K = sblas.kernels
@@ -74,9 +74,9 @@ def test_spmv_vs_oracle(sblas, dev, oracle, dtype, mat, variant):
     drp, dci, dv, dx, dy = (_t(dev, a) for a in (rp, ci, v, x, y0))
     plan = None if variant == "noplan" else K.Plan(drp, len(ci))
     var = dict(auto=0, noplan=0, tile=sblas.SPMV_TILE, vector=sblas.SPMV_VECTOR, split=sblas.SPMV_SPLIT,
-               pipe=sblas.SPMV_PIPE, pipe2=sblas.SPMV_PIPE)[variant]
-    opts = sblas.make_opts(variant=var, tile={"tile": 512, "split": 512, "pipe": 320, "pipe2": 3072}.get(variant, 0),
-                           stages={"pipe": 4, "pipe2": 2}.get(variant, 0))
+               splitp=sblas.SPMV_SPLIT, pipe=sblas.SPMV_PIPE, pipe2=sblas.SPMV_PIPE)[variant]
+    opts = sblas.make_opts(variant=var, tile={"tile": 512, "split": 512, "splitp": 512, "pipe": 320, "pipe2": 3072}.get(variant, 0),
+                           stages={"pipe": 4, "pipe2": 2, "splitp": 2}.get(variant, 0))
     K.spmv(drp, dci, dv, dx, dy, alpha, beta, plan=plan, opts=opts)
     torch.cuda.synchronize()
     bound = _row_bound(oracle, rp, ci, v, x, alpha, beta, y0)
@@ -219,7 +219,8 @@ def _banded_csr(rng, n, bw, dtype, jitter=0):
 @pytest.mark.parametrize("dtype,k", [(np.float64, 64), (np.float64, 256), (np.float64, 100), (np.float64, 300),
                                      (np.float32, 128), (np.float32, 200)])
 @pytest.mark.parametrize("mat", ["banded", "banded_holes", "unsorted", "ragged_tail"])
-def test_spmm_rowblock_bit_identical(sblas, dev, oracle, dtype, k, mat):
+@pytest.mark.parametrize("piped", [False, True])
+def test_spmm_rowblock_bit_identical(sblas, dev, oracle, dtype, k, mat, piped):
     """SBLAS_SPMM_ROWBLOCK: the R x 1 row-block mirror of A (one B load feeds up to R adjacent rows)
     accumulates every row's nonzeros in CSR storage order with rounded mul/add, so it is
     bit-identical to sblas_spmm_csr_cpu (spmm.h:55-68) — also for rows whose columns are unsorted."""
@@ -255,18 +256,26 @@ def test_spmm_rowblock_bit_identical(sblas, dev, oracle, dtype, k, mat):
     else:       # low fill: the mirror is normally dropped (CSR kernel); force it to test the arithmetic
         R, nb, fill = plan.build_rowblocks(dci, dv, R=-4)
         assert nb > 0 and 0.25 <= fill <= 1.0
+    var = sblas.SPMM_ROWBLOCK_PIPE if piped else sblas.SPMM_ROWBLOCK
     K.spmm(drp, dci, dv, k, sblas.ROW_MAJOR, dB, ld, dC, ld, alpha, beta, w, plan=plan,
-           opts=sblas.make_opts(variant=sblas.SPMM_ROWBLOCK))
+           opts=sblas.make_opts(variant=var, stages=3 if k == 100 else 0))
     torch.cuda.synchronize()
     got = _from_rm(dC.cpu().numpy(), h, k, ld)
     assert np.array_equal(got, ref), "k=%d max|d|=%g" % (k, np.abs(got - ref).max())
+    if piped:   # column slices per CTA forced to 1 / 2 / 4 (tile of 8 / 4 / 2 block rows)
+        for P in (1, 2, 4):
+            dCp = _t(dev, _to_rm(C0c, h, k, ld))
+            K.spmm(drp, dci, dv, k, sblas.ROW_MAJOR, dB, ld, dCp, ld, alpha, beta, w, plan=plan,
+                   opts=sblas.make_opts(variant=var, lanes=P,
+                                        flags=sblas.FLAG_PREFETCH_B if P == 2 else sblas.FLAG_NO_PREFETCH_B))
+            assert np.array_equal(_from_rm(dCp.cpu().numpy(), h, k, ld), ref), "P=%d" % P
     # AUTO takes the same path when the plan holds the mirror; FMA flag stays within tolerance
     dC2 = _t(dev, _to_rm(C0c, h, k, ld))
     K.spmm(drp, dci, dv, k, sblas.ROW_MAJOR, dB, ld, dC2, ld, alpha, beta, w, plan=plan)
     assert np.array_equal(_from_rm(dC2.cpu().numpy(), h, k, ld), ref)
     dC3 = _t(dev, _to_rm(C0c, h, k, ld))
     K.spmm(drp, dci, dv, k, sblas.ROW_MAJOR, dB, ld, dC3, ld, alpha, beta, w, plan=plan,
-           opts=sblas.make_opts(variant=sblas.SPMM_ROWBLOCK, flags=sblas.FLAG_FMA))
+           opts=sblas.make_opts(variant=var, flags=sblas.FLAG_FMA))
     got3 = _from_rm(dC3.cpu().numpy(), h, k, ld)
     tol = 1e-12 if dtype == np.float64 else 1e-5
     for n in range(0, k, max(1, k // 7)):
@@ -274,7 +283,8 @@ def test_spmm_rowblock_bit_identical(sblas, dev, oracle, dtype, k, mat):
         assert np.all(np.abs(got3[n * h:(n + 1) * h] - ref[n * h:(n + 1) * h]) <= tol * b)
 
 
-def test_spmm_rowblock_partials_and_replicas(sblas, dev, oracle):
+@pytest.mark.parametrize("piped", [False, True])
+def test_spmm_rowblock_partials_and_replicas(sblas, dev, oracle, piped):
     """HEAD/TAIL partial rows go to the carry buffer, the rest to C and every replica."""
     import torch
     K = sblas.kernels
@@ -291,7 +301,8 @@ def test_spmm_rowblock_partials_and_replicas(sblas, dev, oracle):
     carry = torch.zeros(2 * k, dtype=torch.float64, device=dev)
     plan = K.Plan(drp, len(ci))
     assert plan.build_rowblocks(dci, dv)[1] > 0
-    o = sblas.make_opts(variant=sblas.SPMM_ROWBLOCK, flags=sblas.FLAG_HEAD_PARTIAL | sblas.FLAG_TAIL_PARTIAL,
+    o = sblas.make_opts(variant=sblas.SPMM_ROWBLOCK_PIPE if piped else sblas.SPMM_ROWBLOCK,
+                        flags=sblas.FLAG_HEAD_PARTIAL | sblas.FLAG_TAIL_PARTIAL,
                         replicas=[rep.data_ptr()], carry=carry.data_ptr())
     K.spmm(drp, dci, dv, k, sblas.ROW_MAJOR, dB, k, dC, k, 2.0, 0.5, w, plan=plan, opts=o)
     torch.cuda.synchronize()

@@ -1,0 +1,9 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 600 python -m pytest tests/test_gpu_parity.py -m gpu -q -x --timeout=90 -p no:cacheprovider > gpurun_out/pytest_parity.log 2>&1
+rc=$?; echo "pytest parity exit $rc"; tail -8 gpurun_out/pytest_parity.log
+if [ $rc -ne 0 ]; then exit 1; fi
+timeout 400 python tools/sweep.py --workload b32m --reps 5 --only 4 > gpurun_out/sweep_b32m.log 2>&1; echo "b32m $?"
+timeout 400 python tools/sweep.py --workload c5 --reps 5 --only 4 > gpurun_out/sweep_c5.log 2>&1; echo "c5 $?"
+timeout 400 python tools/sweep.py --workload c3 --reps 3 --only 4 > gpurun_out/sweep_c3.log 2>&1; echo "c3 $?"
+echo finished

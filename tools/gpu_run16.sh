@@ -1,0 +1,11 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 600 python -m pytest tests/test_gpu_parity.py -m gpu -q -x --timeout=90 -p no:cacheprovider -k "spmm" > gpurun_out/pytest_parity.log 2>&1
+rc=$?; echo "pytest parity exit $rc"; tail -8 gpurun_out/pytest_parity.log
+if [ $rc -ne 0 ]; then exit 1; fi
+timeout 400 python tools/sweep.py --workload b32m --reps 5 --only 4 > gpurun_out/sweep_b32m.log 2>&1; echo "b32m $?"
+timeout 400 python tools/sweep.py --workload c5 --reps 5 --only 4 > gpurun_out/sweep_c5.log 2>&1; echo "c5 $?"
+timeout 300 python bench.py --workload b32m --steps 2 --warmup 1 --no-cpu --no-e2e > gpurun_out/plain_b32m.log 2>&1 && \
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:spmm_rbp -s 1 -c 1 -o gpurun_out/prof_b32m_rbp5 -f python bench.py --workload b32m --steps 2 --warmup 1 --no-cpu --no-e2e > gpurun_out/ncu_b32m.log 2>&1
+echo "ncu b32m $?"
+echo finished
