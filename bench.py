@@ -194,6 +194,7 @@ def run_ours(args, wl_key):
     sampler = ClockSampler(torch.cuda.current_device() if world == 1 else local_rank)
     sampler.start()
     cfg_extra = {}
+    opx = None
     if world == 1:
         plan = K.Plan(rp, nnz)
         if op == "spmm":
@@ -257,6 +258,10 @@ def run_ours(args, wl_key):
             opx.exchange(yC)
         loc_rows, loc_nnz, loc_k = r1 - r0, lv.numel(), k
         cfg_extra["stitch"] = stitch
+        # replicated y/C: every GPU must RECEIVE the rows it does not own, whatever the stitch;
+        # at NVLink 5's 900 GB/s per direction that alone takes this long per step
+        cfg_extra["replication_inbound_bytes_per_gpu"] = int((rows - (r1 - r0)) * (ld if op == "spmm" else 1) * esz)
+        cfg_extra["nvlink_floor_ms_per_step"] = cfg_extra["replication_inbound_bytes_per_gpu"] / 900e9 * 1e3
         cfg_extra["panel_rows"] = [int(rb[i + 1] - rb[i]) for i in range(world)]
 
     flush = torch.empty(2 * L2_BYTES // 4, dtype=torch.int32, device=dev)
@@ -317,7 +322,7 @@ def run_ours(args, wl_key):
     ms_other = None
     if world == 1:
         ms_other = float(np.median((timed_flushed if big else timed_region)(step_compute, min(args.steps, 50))))
-    if world > 1 and getattr(opx, "status", None) is not None and int(opx.status.item()) != 0:
+    if opx is not None and getattr(opx, "status", None) is not None and int(opx.status.item()) != 0:
         raise SystemExit("peer barrier timed out waiting for rank %d" % (int(opx.status.item()) - 1))
 
     tot_ms = float(np.sum(ms))

@@ -29,7 +29,8 @@ struct TileTable {
 
 // Row-block (R x 1 BCSR) mirror of A for SpMM, see spmm_rb.cu.  Only materialised when
 // fill = nnz / (n_blocks * R) >= kRowBlockMinFill.
-constexpr double kRowBlockMinFill = 0.5;
+constexpr double kRowBlockMinFill = 0.5;    // R = 4
+constexpr double kRowBlockMinFill8 = 0.7;   // R = 8
 struct RowBlocks {
   int32_t R = 0;
   int64_t n_blockrows = 0;

@@ -268,12 +268,17 @@ static int launch_rb(cudaStream_t st, const sblasPlan_st* plan, int NB, const T*
   const RowBlocks& rb = plan->rb;
   constexpr int BLOCK = 256;
   const int grid = (int)std::min<int64_t>(ceil_div(rb.n_blockrows, BLOCK / 32), (int64_t)kNumSM * 64);
-#define SBLAS_RB(NN)                                                                              \
-  spmm_rb_kernel<T, VEC, NN, 4, EXACT, BLOCK><<<grid, BLOCK, 0, st>>>(                             \
+#define SBLAS_RB(NN, RR)                                                                          \
+  spmm_rb_kernel<T, VEC, NN, RR, EXACT, BLOCK><<<grid, BLOCK, 0, st>>>(                            \
       rb.n_blockrows, rb.d_ptr, (const int2*)rb.d_colmask, (const T*)rb.d_val, B, ldb, sink)
-  if (NB <= 1) SBLAS_RB(1);
-  else if (NB == 2) SBLAS_RB(2);
-  else SBLAS_RB(4);
+  if (rb.R == 8) {  // NB <= 2 (the caller sizes the panels)
+    if (NB <= 1) SBLAS_RB(1, 8);
+    else SBLAS_RB(2, 8);
+  } else {
+    if (NB <= 1) SBLAS_RB(1, 4);
+    else if (NB == 2) SBLAS_RB(2, 4);
+    else SBLAS_RB(4, 4);
+  }
 #undef SBLAS_RB
   SBLAS_LAUNCH_CHECK();
   return 0;
@@ -401,7 +406,7 @@ __device__ __forceinline__ void rbp_blocks(uint32_t a_cm, uint32_t a_val, int n,
 }
 
 template <typename T, int VEC, int NB, int R, bool EXACT, int NSTAGE>
-__global__ void __launch_bounds__(kRbpBlock, NB == 1 ? 3 : 2)
+__global__ void __launch_bounds__(kRbpBlock, (R == 4 ? 4 : 3) - NB)
 spmm_rbp_kernel(int64_t n_blockrows, const int32_t* __restrict__ blk_ptr, const int2* __restrict__ colmask,
                 const T* __restrict__ bval, const T* __restrict__ B, uint32_t ldb_bytes, MatSink<T> sink,
                 int32_t cap_blocks, int32_t kp, int32_t logP, int32_t prefetch) {
@@ -558,21 +563,24 @@ spmm_rbp_kernel(int64_t n_blockrows, const int32_t* __restrict__ blk_ptr, const 
 }
 
 // P = column slices per CTA (1, 2, 4); panel = P*NB*32*VEC columns per pass over A
-template <typename T, int VEC, bool EXACT>
-static int launch_rbp(cudaStream_t st, const sblasPlan_st* plan, int NB, int logP, int stages, const T* B,
-                      int64_t ldb, const MatSink<T>& sink, int32_t kp) {
+template <typename T, int VEC, bool EXACT, int R>
+static int launch_rbp_r(cudaStream_t st, const sblasPlan_st* plan, int NB, int logP, int stages, const T* B,
+                        int64_t ldb, const MatSink<T>& sink, int32_t kp) {
   const RowBlocks& rb = plan->rb;
-  constexpr int R = 4;
   const int W = kRbpConsumers >> logP;
   const int32_t tile_blocks = logP == 0 ? rb.max_tile_blocks : logP == 1 ? rb.max_tile_blocks4 : rb.max_tile_blocks2;
   const int32_t cap_blocks = (tile_blocks + 2 + 1) & ~1;
+  auto smem_for = [&](int n) {
+    return kRbpHeader + n * rbp_stage_bytes<T, R>(cap_blocks) + (size_t)kRbpConsumers * rbp_cbuf_bytes<R>(NB <= 1 ? 1 : 2);
+  };
+  // 3 stages only on request, for R = 4, and only while 2 CTAs still fit an SM
+  const int ns = (stages >= 3 && R == 4 && smem_for(3) <= 100 * 1024) ? 3 : 2;
   const void* kern;
-  if (stages <= 2) kern = NB <= 1 ? (const void*)spmm_rbp_kernel<T, VEC, 1, R, EXACT, 2>
-                                  : (const void*)spmm_rbp_kernel<T, VEC, 2, R, EXACT, 2>;
-  else kern = NB <= 1 ? (const void*)spmm_rbp_kernel<T, VEC, 1, R, EXACT, 3>
-                      : (const void*)spmm_rbp_kernel<T, VEC, 2, R, EXACT, 3>;
-  const int ns = stages <= 2 ? 2 : 3;
-  const size_t smem = kRbpHeader + ns * rbp_stage_bytes<T, R>(cap_blocks) + (size_t)kRbpConsumers * rbp_cbuf_bytes<R>(NB <= 1 ? 1 : 2);
+  if (ns == 2) kern = NB <= 1 ? (const void*)spmm_rbp_kernel<T, VEC, 1, R, EXACT, 2>
+                              : (const void*)spmm_rbp_kernel<T, VEC, 2, R, EXACT, 2>;
+  else kern = NB <= 1 ? (const void*)spmm_rbp_kernel<T, VEC, 1, R, EXACT, R == 4 ? 3 : 2>
+                      : (const void*)spmm_rbp_kernel<T, VEC, 2, R, EXACT, R == 4 ? 3 : 2>;
+  const size_t smem = smem_for(ns);
   SBLAS_CHECK(smem <= 200 * 1024, "spmm rowblock pipe: tile needs %zu bytes of shared memory", smem);
   if (smem > 48 * 1024) SBLAS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = 0;
@@ -592,6 +600,25 @@ static int launch_rbp(cudaStream_t st, const sblasPlan_st* plan, int NB, int log
   SBLAS_CUDA(cudaLaunchKernel(kern, dim3(grid), dim3(kRbpBlock), args, smem, st));
   ++g_launches;
   return 0;
+}
+
+// shared memory the pipelined kernel needs for this plan (2 stages); it falls back to the
+// unpiped kernel when a tile of the mirror does not fit
+template <typename T>
+static size_t rbp_smem_bytes(const sblasPlan_st* plan, int NB, int logP) {
+  const RowBlocks& rb = plan->rb;
+  const int32_t tile_blocks = logP == 0 ? rb.max_tile_blocks : logP == 1 ? rb.max_tile_blocks4 : rb.max_tile_blocks2;
+  const int32_t cap_blocks = (tile_blocks + 2 + 1) & ~1;
+  const size_t stage = rb.R == 8 ? rbp_stage_bytes<T, 8>(cap_blocks) : rbp_stage_bytes<T, 4>(cap_blocks);
+  const size_t cbuf = rb.R == 8 ? rbp_cbuf_bytes<8>(NB <= 1 ? 1 : 2) : rbp_cbuf_bytes<4>(NB <= 1 ? 1 : 2);
+  return kRbpHeader + 2 * stage + (size_t)kRbpConsumers * cbuf;
+}
+
+template <typename T, int VEC, bool EXACT>
+static int launch_rbp(cudaStream_t st, const sblasPlan_st* plan, int NB, int logP, int stages, const T* B,
+                      int64_t ldb, const MatSink<T>& sink, int32_t kp) {
+  return plan->rb.R == 8 ? launch_rbp_r<T, VEC, EXACT, 8>(st, plan, NB, logP, stages, B, ldb, sink, kp)
+                         : launch_rbp_r<T, VEC, EXACT, 4>(st, plan, NB, logP, stages, B, ldb, sink, kp);
 }
 
 // ---- COLMAJOR ---------------------------------------------------------------------------------
@@ -751,23 +778,22 @@ static int spmm_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
       rc = 2;
     }
     if (rc == 0 && rb_ok && (want == SBLAS_VARIANT_AUTO || want == SBLAS_SPMM_ROWBLOCK || want == SBLAS_SPMM_ROWBLOCK_PIPE)) {
-      // pipelined flavour: needs the tile statistics and a B pitch below 4 GB.  One pass over A
-      // covers P*NB slices of 32*VF columns: (NB, P) = (1,1) (2,1) (2,2) for 1, 2, 3-4 slices;
-      // opts->lanes = 1/2/4 forces P.  AUTO takes it; SBLAS_SPMM_ROWBLOCK keeps the unpiped kernel.
-      const bool piped = want != SBLAS_SPMM_ROWBLOCK && plan->rb.max_tile_blocks > 0 &&
-                         ldb * (int64_t)sizeof(T) < (1ll << 32);
+      // pipelined flavour: needs the tile statistics and a B pitch below 4 GB.  A pass over A covers
+      // P*NB slices of 32*VF columns.  AUTO: P = 1 (tiles of 8 block rows keep the most B rows
+      // in L1) and NB = 2 as soon as there are two slices, i.e. k = 256 fp64 takes two passes
+      // (7.3 ms on config 5 against 8.4 / 8.7 ms for one pass with P = 2 / 4); opts->lanes =
+      // 1/2/4 forces P.  SBLAS_SPMM_ROWBLOCK keeps the unpiped kernel.
+      bool piped = want != SBLAS_SPMM_ROWBLOCK && plan->rb.max_tile_blocks > 0 &&
+                   ldb * (int64_t)sizeof(T) < (1ll << 32);
       const int slice = 32 * VF;
       int NBp = 1, logP = 0;
       if (piped) {
         const int n_slices = (k + slice - 1) / slice;
-        if (n_slices >= 3) { NBp = 2; logP = 1; }
-        else if (n_slices == 2) { NBp = 2; logP = 0; }
-        if (o && (o->lanes == 1 || o->lanes == 2 || o->lanes == 4)) {
-          logP = o->lanes == 1 ? 0 : o->lanes == 2 ? 1 : 2;
-          NBp = n_slices > (1 << logP) ? 2 : 1;
-        }
+        if (o && (o->lanes == 1 || o->lanes == 2 || o->lanes == 4)) logP = o->lanes == 1 ? 0 : o->lanes == 2 ? 1 : 2;
+        NBp = n_slices > (1 << logP) ? 2 : 1;
       }
-      const int rbpanel = piped ? slice * NBp * (1 << logP) : slice * 4;
+      if (piped && rbp_smem_bytes<T>(plan, NBp, logP) > 100 * 1024) piped = false;  // >= 2 CTAs per SM or not at all
+      const int rbpanel = piped ? slice * NBp * (1 << logP) : slice * (plan->rb.R == 8 ? 2 : 4);
       for (int32_t c_off = 0; c_off < k && rc == 0; c_off += rbpanel) {
         const int kp = std::min<int32_t>(rbpanel, k - c_off);
         const int NB = (kp + 32 * VF - 1) / (32 * VF);

@@ -74,7 +74,8 @@ __global__ void rb_tile_max_kernel(const int32_t* __restrict__ blk_ptr, int64_t 
 }
 
 template <typename T, int R>
-static int build_rowblocks(cudaStream_t st, sblasPlan_st* plan, const int32_t* ci, const T* val, bool force) {
+static int build_rowblocks(cudaStream_t st, sblasPlan_st* plan, const int32_t* ci, const T* val, bool force,
+                           double min_fill) {
   const int64_t nbr = ((int64_t)plan->rows + R - 1) / R;
   RowBlocks& rb = plan->rb;
   int32_t* counts = nullptr;
@@ -98,7 +99,7 @@ static int build_rowblocks(cudaStream_t st, sblasPlan_st* plan, const int32_t* c
   rb.n_blocks = total;
   rb.is_f64 = sizeof(T) == 8;
   rb.fill = total > 0 ? (double)plan->nnz / ((double)total * R) : 0.0;
-  if (rb.fill < kRowBlockMinFill && !force) {  // does not pay: keep only the statistic
+  if (rb.fill < min_fill && !force) {  // does not pay: keep only the statistic
     SBLAS_CUDA(cudaFree(counts));
     SBLAS_CUDA(cudaFree(rb.d_ptr));
     rb.d_ptr = nullptr;
@@ -128,16 +129,21 @@ static int build_rowblocks(cudaStream_t st, sblasPlan_st* plan, const int32_t* c
   return 0;
 }
 
+// R = 0 (what sync2gpu asks for): R = 4, kept when its fill reaches kRowBlockMinFill.  R = 4 / 8:
+// that height or nothing (R = 8 needs fill >= kRowBlockMinFill8; measured no faster than R = 4
+// on the banded inputs — 9.9 against 8.8 ms on b32m, 8.0 against 7.3 ms on config 5 — so it is
+// never chosen automatically).  R < 0: |R|, kept whatever the fill (tests).
 template <typename T>
 static int build_impl(cudaStream_t st, sblasPlan_st* plan, const int32_t* ci, const T* val, int32_t R) {
   SBLAS_CHECK(plan && (plan->nnz == 0 || (ci && val)), "plan_build_rowblocks: null argument");
   rowblocks_free(plan);
   if (plan->rows == 0 || plan->nnz == 0) return 0;
-  const bool force = R < 0;  // keep the mirror whatever the fill (tests)
+  const bool force = R < 0;
   if (R < 0) R = -R;
-  if (R == 0) R = 4;
-  SBLAS_CHECK(R == 4, "plan_build_rowblocks: only R = 4 is built");
-  return build_rowblocks<T, 4>(st, plan, ci, val, force);
+  SBLAS_CHECK(R == 0 || R == 4 || R == 8, "plan_build_rowblocks: R must be 0 (auto), 4 or 8");
+  if (R == 8) return build_rowblocks<T, 8>(st, plan, ci, val, force, kRowBlockMinFill8);
+  if (R == 4) return build_rowblocks<T, 4>(st, plan, ci, val, force, kRowBlockMinFill);
+  return build_rowblocks<T, 4>(st, plan, ci, val, false, kRowBlockMinFill);
 }
 
 void rowblocks_free(sblasPlan_st* plan) {

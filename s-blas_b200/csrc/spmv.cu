@@ -22,7 +22,8 @@
 namespace sblas {
 
 constexpr int kSpmvBlock = 256;
-constexpr int kSpmvDefaultTile = 3072;      // TILE / SPLIT
+constexpr int kSpmvDefaultTile = 3072;      // TILE
+constexpr int kSpmvSplitDefaultTile = 1536; // SPLIT: config 4 0.66 ms (1536-2048) against 1.5 ms at 3072 and up
 constexpr int kSpmvPipeDefaultTile = 1536;  // PIPE: small tiles, 2 stages -> most resident CTAs (sweeps, profiles/)
 constexpr int kSpmvMaxSmem = 96 * 1024;
 constexpr int kSpmvPipeMaxRow = 4096;       // longest row PIPE stages whole (2 stages <= ~200 KB)
@@ -765,6 +766,7 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
     }
   }
   if (rc == 0 && variant == SBLAS_SPMV_SPLIT) {
+    if (!(o && o->tile > 0)) tile = kSpmvSplitDefaultTile;
     // table (row_weight = -1) marks the merge-path split table; built here, cached in the plan
     const TileTable* tt = nullptr;
     for (const TileTable& t : plan->tables)

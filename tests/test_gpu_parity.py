@@ -220,7 +220,8 @@ def _banded_csr(rng, n, bw, dtype, jitter=0):
                                      (np.float32, 128), (np.float32, 200)])
 @pytest.mark.parametrize("mat", ["banded", "banded_holes", "unsorted", "ragged_tail"])
 @pytest.mark.parametrize("piped", [False, True])
-def test_spmm_rowblock_bit_identical(sblas, dev, oracle, dtype, k, mat, piped):
+@pytest.mark.parametrize("R", [4, 8])
+def test_spmm_rowblock_bit_identical(sblas, dev, oracle, dtype, k, mat, piped, R):
     """SBLAS_SPMM_ROWBLOCK: the R x 1 row-block mirror of A (one B load feeds up to R adjacent rows)
     accumulates every row's nonzeros in CSR storage order with rounded mul/add, so it is
     bit-identical to sblas_spmm_csr_cpu (spmm.h:55-68) — also for rows whose columns are unsorted."""
@@ -250,12 +251,12 @@ def test_spmm_rowblock_bit_identical(sblas, dev, oracle, dtype, k, mat, piped):
     dB, dC = _t(dev, _to_rm(Bc, w, k, ld)), _t(dev, _to_rm(C0c, h, k, ld))
     drp, dci, dv = (_t(dev, a) for a in (rp, ci, v))
     plan = K.Plan(drp, len(ci))
-    R, nb, fill = plan.build_rowblocks(dci, dv)
-    if mat in ("banded", "banded_holes"):
-        assert R == 4 and nb > 0 and 0.5 <= fill <= 1.0
-    else:       # low fill: the mirror is normally dropped (CSR kernel); force it to test the arithmetic
-        R, nb, fill = plan.build_rowblocks(dci, dv, R=-4)
-        assert nb > 0 and 0.25 <= fill <= 1.0
+    Rr, nb, fill = plan.build_rowblocks(dci, dv, R=R)
+    if mat == "banded":
+        assert Rr == R and nb > 0 and (0.7 if R == 8 else 0.5) <= fill <= 1.0
+    if nb == 0:  # low fill: the mirror is normally dropped (CSR kernel); force it to test the arithmetic
+        Rr, nb, fill = plan.build_rowblocks(dci, dv, R=-R)
+    assert Rr == R and nb > 0 and 1.0 / R <= fill <= 1.0
     var = sblas.SPMM_ROWBLOCK_PIPE if piped else sblas.SPMM_ROWBLOCK
     K.spmm(drp, dci, dv, k, sblas.ROW_MAJOR, dB, ld, dC, ld, alpha, beta, w, plan=plan,
            opts=sblas.make_opts(variant=var, stages=3 if k == 100 else 0))
@@ -281,6 +282,23 @@ def test_spmm_rowblock_bit_identical(sblas, dev, oracle, dtype, k, mat, piped):
     for n in range(0, k, max(1, k // 7)):
         b = _row_bound(oracle, rp, ci, v, Bc[n * w:(n + 1) * w], alpha, beta, C0c[n * h:(n + 1) * h])
         assert np.all(np.abs(got3[n * h:(n + 1) * h] - ref[n * h:(n + 1) * h]) <= tol * b)
+
+
+def test_rowblock_height_selection(sblas, dev):
+    """R = 0 (what sync2gpu asks for): the R = 4 mirror when its fill pays, else no mirror."""
+    K = sblas.kernels
+    rng = np.random.default_rng(5)
+    for kind, want in (("band", 4), ("holes", 4), ("random", 0)):
+        if kind == "band":
+            rp, ci, v = _banded_csr(rng, 600, 24, np.float64)
+        elif kind == "holes":
+            rp, ci, v = _banded_csr(rng, 600, 6, np.float64, jitter=0.25)
+        else:
+            rp, ci, v = _rand_csr(rng, 600, 600, 8, 0.0, None, np.float64)
+        drp, dci, dv = (_t(dev, a) for a in (rp, ci, v))
+        plan = K.Plan(drp, len(ci))
+        R, nb, fill = plan.build_rowblocks(dci, dv)
+        assert (R if nb else 0) == want, (kind, R, nb, fill)
 
 
 @pytest.mark.parametrize("piped", [False, True])

@@ -1,0 +1,9 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests/test_gpu_parity.py -m gpu -q -x --timeout=120 -p no:cacheprovider -k "rowblock" > gpurun_out/pytest_rb.log 2>&1
+rc=$?; echo "pytest rb exit $rc"; tail -12 gpurun_out/pytest_rb.log
+for rb in 8 4; do
+timeout 400 python tools/sweep.py --workload b32m --reps 5 --only 4 --rb $rb > gpurun_out/sweep_b32m_r$rb.log 2>&1; echo "b32m $?"
+timeout 400 python tools/sweep.py --workload c5 --reps 5 --only 4 --rb $rb > gpurun_out/sweep_c5_r$rb.log 2>&1; echo "c5 $?"
+done
+echo finished

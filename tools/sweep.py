@@ -27,6 +27,7 @@ def main():
     ap.add_argument("--out", default=None)
     ap.add_argument("--dirty-flush", action="store_true")
     ap.add_argument("--only", type=int, default=None, help="only this variant")
+    ap.add_argument("--rb", type=int, default=0, help="row-block height of the SpMM mirror (0 = auto, 4, 8)")
     args = ap.parse_args()
     import torch
     import __graft_entry__ as ge
@@ -52,7 +53,7 @@ def main():
         grid = [dict(variant=0)]
         grid += [dict(variant=pkg.SPMV_TILE, tile=t, lanes=l) for t in (1024, 1536, 2048, 3072, 4096, 6144, 8192)
                  for l in ((0,) if args.grid == "default" else (0, 1, 2, 4, 8, 16, 32))]
-        grid += [dict(variant=pkg.SPMV_SPLIT, tile=t, stages=st) for t in (1024, 1536, 2048, 3072, 4096) for st in (2, 3)]
+        grid += [dict(variant=pkg.SPMV_SPLIT, tile=t, stages=st) for t in (512, 1024, 1536, 2048, 3072, 4096, 6144) for st in (0, 2)]
         grid += [dict(variant=pkg.SPMV_PIPE, tile=t, stages=st, lanes=l) for t in (1536, 2048, 3072, 4096, 6144, 8192) for st in (2, 3, 4)
                  for l in ((0,) if args.grid == 'default' else (0, 1, 2, 4, 8, 16))]
         grid += [dict(variant=pkg.SPMV_VECTOR, lanes=l, flags=f) for l in (1, 2, 4, 8, 16, 32) for f in (0, 1)]
@@ -60,7 +61,7 @@ def main():
         grid = [dict(tile=t, flags=f, lanes=l) for t in (256, 512, 1024, 2048, 4096, 16384) for f in (0, 1)
                 for l in ((0,) if args.grid == "default" else (0, 32))]
     if wl['op'] == 'spmm':
-        print('rowblocks', plan.build_rowblocks(ci, v), flush=True)
+        print('rowblocks', plan.build_rowblocks(ci, v, R=args.rb), flush=True)
         grid = [dict(variant=pkg.SPMM_ROWBLOCK_PIPE, flags=f, stages=st, lanes=P) for f in (0, 1) for st in (2,) for P in (1, 2, 4)] + [dict(variant=pkg.SPMM_ROWBLOCK, flags=f) for f in (0, 1)] + [dict(variant=pkg.SPMM_ROWMAJOR, tile=t, flags=f) for t in (512, 2048) for f in (0, 1)]
     res = []
     if args.only is not None:
