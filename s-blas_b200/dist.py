@@ -97,6 +97,24 @@ class IpcBuffer:
                 self.ptr = C.c_void_p()
 
 
+class SymmBuffer:
+    """Output replica in torch symmetric memory (torch.distributed._symmetric_memory, CUDA backend):
+    every rank maps every peer's buffer AND, on an NVSwitch box, one multicast address whose stores
+    the switch replicates into all ranks' buffers (NVLS).  `mc_ptr` is 0 where the box has no
+    multicast support; `peer_ptrs` always works (the same role as IpcBuffer.peer_ptrs)."""
+
+    def __init__(self, numel, dtype, device):
+        import torch.distributed._symmetric_memory as symm_mem
+        dist = _dist()
+        self.t = symm_mem.empty(int(numel), dtype=dtype, device=device)
+        self.hdl = symm_mem.rendezvous(self.t, dist.group.WORLD)
+        self.peer_ptrs = [int(p) for p in self.hdl.buffer_ptrs]
+        self.mc_ptr = int(self.hdl.multicast_ptr) if getattr(self.hdl, "has_multicast_support", True) else 0
+
+    def tensor(self):
+        return self.t
+
+
 class RowSplitOp:
     """y/C <- beta*y/C + alpha*A*x/B with A split into row panels across the ranks.
 
@@ -105,7 +123,7 @@ class RowSplitOp:
     view of an IpcBuffer whose peers have been opened (pass peer_ptrs)."""
 
     def __init__(self, rows_total, cols, row_begin, rp, ci, val, k=1, ld=1, stitch="nccl",
-                 peer_ptrs=None, plan=None):
+                 peer_ptrs=None, plan=None, mc_ptr=0):
         dist = _dist()
         self.rank = dist.get_rank() if dist.is_initialized() else 0
         self.world = dist.get_world_size() if dist.is_initialized() else 1
@@ -119,11 +137,20 @@ class RowSplitOp:
         self.equal = len({self.row_begin[i + 1] - self.row_begin[i] for i in range(self.world)}) == 1
         self.opts = None
         self.flags = None
-        if self.stitch == "peer":
+        if self.stitch == "mc":
+            # one store per finished row slice into the multicast address: the NVSwitch replicates it
+            # into every rank's buffer (this rank's included), so a GPU sends |panel| bytes, not (n-1)x
+            if not mc_ptr:
+                raise RuntimeError("stitch='mc' needs a multicast address (SymmBuffer.mc_ptr is 0 on this box)")
+            self.opts = make_opts(replicas=[mc_ptr + self.r0 * ld * val.element_size()])
+            self.stitch = "peer"            # same device-side barrier closes the step
+            peer_ptrs = None
+        elif self.stitch == "peer":
             esz = val.element_size()
             off = self.r0 * ld * esz
             reps = [p + off for r, p in enumerate(peer_ptrs) if r != self.rank]
             self.opts = make_opts(replicas=reps)
+        if self.stitch == "peer":
             # flag words of the device-side barrier that completes the step (sblas_peer_barrier)
             import torch
             self.flags = IpcBuffer(256, val.device)
