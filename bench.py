@@ -177,6 +177,8 @@ def run_ours(args, wl_key):
     tdtype = torch.float64 if f64 else torch.float32
     esz = 8 if f64 else 4
     k = wl.get("k", 1)
+    if args.k and wl["op"] == "spmm":
+        k = args.k
     # weak scaling for the SpMV workloads (per-GPU rows fixed), strong for the fixed SpMM configs
     scaling = args.scaling or ("weak" if op == "spmv" else "strong")
     if world > 1 and scaling == "weak":
@@ -431,6 +433,18 @@ def run_ours(args, wl_key):
         cpu = cpu_baseline(wl_key, wl, op, f64, k, rp, ci, v, cols, budget_s=args.cpu_seconds)
 
     traffic, traffic_src, kernel_name = ncu_traffic(wl_key, world, args)
+    # second roof of the SpMM workloads (config 5 sits at the FP64 ridge): the box's
+    # FP64 multiply-add issue rate, measured here with the library's calibration kernel, in the
+    # arithmetic mode the run used (bit-exact = DMUL + DADD per multiply-add, SBLAS_FLAG_FMA = DFMA)
+    fp64 = None
+    if op == "spmm" and f64:
+        fp64 = fp64_roof(L, torch, dev)
+        rate = fp64["fma_tmac_per_s"] if (args.flags & pkg.FLAG_FMA) else fp64["mul_add_tmac_per_s"]
+        t_fp = loc_nnz * loc_k / (rate * 1e12) * 1e3
+        t_hbm = abytes / (peak * 1e9) * 1e3
+        fp64.update({"mode": "fma" if (args.flags & pkg.FLAG_FMA) else "mul+add (bit-exact)",
+                     "fp64_floor_ms": t_fp, "hbm_floor_ms": t_hbm,
+                     "frac_of_binding_roof": max(t_fp, t_hbm) / (tot_k_ms / args.steps)})
     if rank == 0:
         out = {
             "metric": "CSR SpMV/SpMM GFLOP/s and % of HBM roofline at 1/2/4/8 B200 vs reference CPU",
@@ -459,6 +473,8 @@ def run_ours(args, wl_key):
                          "gather_model_bytes_per_launch": int(gather_bytes(op, loc_rows, cols, loc_nnz, loc_k, esz)),
                          "kernel": kernel_name},
         }
+        if fp64:
+            out["roofline"]["fp64"] = fp64
         if e2e:
             out["e2e"] = e2e
         if cpu:
@@ -467,6 +483,30 @@ def run_ours(args, wl_key):
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def fp64_roof(L, torch, dev):
+    """FP64 multiply-adds per second of this GPU: DFMA chains and DMUL+DADD chains (sblas_fp64_rate)."""
+    import ctypes as C
+    out = torch.zeros(1, dtype=torch.float64, device=dev)
+    grid, iters = 148 * 8, 4096
+    macs = grid * 256 * 8 * iters
+    res = {}
+    for mode, key in ((0, "fma_tmac_per_s"), (1, "mul_add_tmac_per_s")):
+        best = None
+        for _ in range(4):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            rc = L.sblas_fp64_rate(C.c_void_p(torch.cuda.current_stream().cuda_stream), C.c_int32(mode),
+                                   C.c_int32(grid), C.c_int32(iters), C.c_void_p(out.data_ptr()))
+            b.record()
+            torch.cuda.synchronize()
+            if rc != 0:
+                raise SystemExit("sblas_fp64_rate failed")
+            t = a.elapsed_time(b)
+            best = t if best is None else min(best, t)
+        res[key] = macs / (best * 1e-3) / 1e12
+    return res
 
 
 def ncu_traffic(wl_key, world, args):
@@ -666,6 +706,7 @@ def main():
     ap.add_argument("--tile", type=int, default=0)
     ap.add_argument("--lanes", type=int, default=0)
     ap.add_argument("--stages", type=int, default=0)
+    ap.add_argument("--k", type=int, default=0, help="override the dense width of an SpMM workload (experiments)")
     ap.add_argument("--flags", type=int, default=0)
     ap.add_argument("--scale-down", type=int, default=1, help="shrink the workload (smoke runs)")
     ap.add_argument("--no-e2e", action="store_true")

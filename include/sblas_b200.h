@@ -180,6 +180,10 @@ SBLAS_API int sblas_axpby_f32(void* stream, float* d_v0, const float* d_v1, floa
 /* kernel.h:19-25 denseVector_plusEqual_scalar (with the index bug at :22 fixed):
  * v[i] = v[i]*beta + val. */
 SBLAS_API int sblas_scal_add_f64(void* stream, double* d_v, double val, double beta, int64_t n);
+/* calibration: grid*256 threads each run 8 chains of `iters` fp64 multiply-adds (mode 0: DFMA,
+   mode 1: separately rounded DMUL + DADD as the bit-exact SpMM path issues them); time it with
+   events to get the FP64 roof beside the HBM one */
+SBLAS_API int sblas_fp64_rate(void* stream, int32_t mode, int32_t grid, int32_t iters, double* d_out);
 SBLAS_API int sblas_scal_add_f32(void* stream, float* d_v, float val, float beta, int64_t n);
 
 /* out[b*out_ld + a] = in[a*in_ld + b], a < n_major, b < n_minor.  Converts the reference's

@@ -103,7 +103,33 @@ static int transpose_impl(cudaStream_t st, const T* in, int64_t in_ld, int64_t n
 }  // namespace sblas
 
 using namespace sblas;
+// ---- FP64 issue-rate calibration (bench.py: the second roof of the SpMM workloads) -------------
+// MODE 0: chains of DFMA; MODE 1: chains of separately rounded DMUL + DADD (what the exact SpMM
+// path issues per multiply-add).  8 independent chains per thread, `iters` steps each.
+template <int MODE>
+__global__ void __launch_bounds__(256) fp64_rate_kernel(int iters, double seed, double* out) {
+  double a[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) a[j] = seed + j + threadIdx.x * 1e-9;
+  const double m = 1.0 + seed * 1e-12, c = seed * 1e-13;
+  for (int i = 0; i < iters; ++i) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a[j] = MODE == 0 ? fma_rn(a[j], m, c) : add_rn(mul_rn(a[j], m), c);
+  }
+  double s = 0;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s += a[j];
+  if (s == 12345.678) out[0] = s;  // never true: keeps the chains alive
+}
+
 extern "C" {
+// multiply-adds issued = grid*256*8*iters; time it with events around the call (bench.py)
+int sblas_fp64_rate(void* s, int32_t mode, int32_t grid, int32_t iters, double* d_out) {
+  if (mode == 0) fp64_rate_kernel<0><<<grid, 256, 0, (cudaStream_t)s>>>(iters, 1.25, d_out);
+  else fp64_rate_kernel<1><<<grid, 256, 0, (cudaStream_t)s>>>(iters, 1.25, d_out);
+  SBLAS_LAUNCH_CHECK();
+  return 0;
+}
 int sblas_axpby_f64(void* s, double* v0, const double* v1, double a, double b, int64_t n) {
   return axpby_impl<double>((cudaStream_t)s, v0, v1, a, b, n);
 }

@@ -770,11 +770,11 @@ static int spmm_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
     const int VEC = vec ? VF : 1;
     // row-block mirror (R x 1 BCSR, built by sblas_plan_build_rowblocks_*): one B load feeds up to
     // R adjacent rows.  Taken when the plan holds it for this value type, the operands are
-    // vectorisable and a row slice spans a whole warp (k >= 32*VEC); AUTO or SBLAS_SPMM_ROWBLOCK.
+    // vectorisable and a row slice keeps at least half a warp busy (k >= 16*VEC); AUTO or SBLAS_SPMM_ROWBLOCK.
     const int want = o ? o->variant : SBLAS_VARIANT_AUTO;
-    const bool rb_ok = vec && plan->rb.n_blocks > 0 && plan->rb.is_f64 == (sizeof(T) == 8) && k >= 32 * VF;
+    const bool rb_ok = vec && plan->rb.n_blocks > 0 && plan->rb.is_f64 == (sizeof(T) == 8) && k >= 16 * VF;
     if ((want == SBLAS_SPMM_ROWBLOCK || want == SBLAS_SPMM_ROWBLOCK_PIPE) && !rb_ok) {
-      set_error("spmm: SBLAS_SPMM_ROWBLOCK needs a plan with row blocks of this value type, 16-byte aligned operands and k >= %d", 32 * VF);
+      set_error("spmm: SBLAS_SPMM_ROWBLOCK needs a plan with row blocks of this value type, 16-byte aligned operands and k >= %d", 16 * VF);
       rc = 2;
     }
     if (rc == 0 && rb_ok && (want == SBLAS_VARIANT_AUTO || want == SBLAS_SPMM_ROWBLOCK || want == SBLAS_SPMM_ROWBLOCK_PIPE)) {

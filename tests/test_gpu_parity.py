@@ -217,7 +217,7 @@ def _banded_csr(rng, n, bw, dtype, jitter=0):
 
 
 @pytest.mark.parametrize("dtype,k", [(np.float64, 64), (np.float64, 256), (np.float64, 100), (np.float64, 300),
-                                     (np.float32, 128), (np.float32, 200)])
+                                     (np.float64, 40), (np.float32, 128), (np.float32, 200), (np.float32, 72)])
 @pytest.mark.parametrize("mat", ["banded", "banded_holes", "unsorted", "ragged_tail"])
 @pytest.mark.parametrize("piped", [False, True])
 @pytest.mark.parametrize("R", [4, 8])
