@@ -57,8 +57,12 @@ enum {
   SBLAS_SPMM_ROWBLOCK = 3, /* row-major B/C on the plan's R x 1 row-block mirror of A: one B load feeds
                               up to R adjacent rows (structured inputs); needs
                               sblas_plan_build_rowblocks_* */
-  SBLAS_SPMM_ROWBLOCK_PIPE = 4 /* the same on persistent CTAs: mirror ranges and old C rows of the next
-                              tiles staged by TMA bulk copies behind mbarriers (AUTO's choice) */
+  SBLAS_SPMM_ROWBLOCK_PIPE = 4, /* the same on persistent CTAs (producer warp + 8 consumer warps): mirror
+                              ranges of the next tiles staged by TMA bulk copies behind mbarriers (AUTO's choice
+                              when the plan holds the mirror) */
+  SBLAS_SPMM_ROWBLOCK_TILEB = 5 /* ... and the DISTINCT B rows of every tile staged once by TMA too (the
+                              mirror's tile column lists; rows with ascending columns, lists that fit
+                              shared memory).  On request only: measured level with ROWBLOCK_PIPE */
 };
 enum {
   SBLAS_FLAG_FMA = 1,          /* allow fused multiply-add (default: separately rounded mul/add

@@ -14,7 +14,7 @@ Layout:
 """
 from . import _lib, dist, kernels, matrix, ops, synth, synth_np  # noqa: F401
 from ._lib import (COL_MAJOR, FLAG_FMA, FLAG_HEAD_PARTIAL, FLAG_NO_L1, FLAG_NO_PREFETCH_B, FLAG_PREFETCH_B, FLAG_TAIL_PARTIAL,  # noqa: F401
-                   ROW_MAJOR, SPMM_COLMAJOR, SPMM_ROWBLOCK, SPMM_ROWBLOCK_PIPE, SPMM_ROWMAJOR, SPMV_PIPE, SPMV_SPLIT, SPMV_TILE, SPMV_VECTOR,
+                   ROW_MAJOR, SPMM_COLMAJOR, SPMM_ROWBLOCK, SPMM_ROWBLOCK_PIPE, SPMM_ROWBLOCK_TILEB, SPMM_ROWMAJOR, SPMV_PIPE, SPMV_SPLIT, SPMV_TILE, SPMV_VECTOR,
                    SblasError, make_opts)
 from .matrix import (CsrSparseMatrix, DenseMatrix, DenseVector, col_major, none, replicate,  # noqa: F401
                      row_major, segment)

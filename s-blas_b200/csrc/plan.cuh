@@ -31,6 +31,7 @@ struct TileTable {
 // fill = nnz / (n_blocks * R) >= kRowBlockMinFill.
 constexpr double kRowBlockMinFill = 0.5;    // R = 4
 constexpr double kRowBlockMinFill8 = 0.7;   // R = 8
+constexpr int kRbMaskBits = 0xff;           // presence mask = low byte of colmask.y
 struct RowBlocks {
   int32_t R = 0;
   int64_t n_blockrows = 0;
@@ -43,6 +44,12 @@ struct RowBlocks {
   int32_t* d_ptr = nullptr;      // [n_blockrows + 1] first block of each block row
   void* d_colmask = nullptr;     // int2 {col, presence mask} per block
   void* d_val = nullptr;         // T[n_blocks * R], 0 where absent
+  // tile column lists (tiles of 8 block rows, rows with ascending columns only): the distinct
+  // columns of a tile, ascending; block b of the tile carries the position of its column in
+  // that list in bits 9.. of colmask[b].y.  The TILEB kernel stages those B rows once per tile.
+  int32_t* d_tile_colptr = nullptr;  // [n_tiles8 + 1]
+  int32_t* d_tile_cols = nullptr;
+  int32_t max_tile_cols = 0;         // 0: no lists (unsorted rows, or not built)
 };
 
 }  // namespace sblas

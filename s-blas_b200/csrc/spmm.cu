@@ -372,7 +372,7 @@ __device__ __forceinline__ void rbp_blocks(uint32_t a_cm, uint32_t a_val, int n,
       mask[u] = 0;
     } else {
       const int2 cm = lds_i2(a_cm + u * 8);
-      mask[u] = cm.y;
+      mask[u] = cm.y & kRbMaskBits;
       const uint64_t roff = (uint64_t)(uint32_t)cm.x * ldb_bytes;
 #pragma unroll
       for (int nb = 0; nb < NB; ++nb) bv[u][nb] = ldg_v(reinterpret_cast<const V*>(bb[nb] + roff));
@@ -573,13 +573,16 @@ static int launch_rbp_r(cudaStream_t st, const sblasPlan_st* plan, int NB, int l
   auto smem_for = [&](int n) {
     return kRbpHeader + n * rbp_stage_bytes<T, R>(cap_blocks) + (size_t)kRbpConsumers * rbp_cbuf_bytes<R>(NB <= 1 ? 1 : 2);
   };
-  // 3 stages only on request, for R = 4, and only while 2 CTAs still fit an SM
-  const int ns = (stages >= 3 && R == 4 && smem_for(3) <= 100 * 1024) ? 3 : 2;
+  // stages of the A mirror in flight (2..4; R = 8 mirrors: 2), while 2 CTAs still fit an SM
+  int ns = R == 4 ? std::min(std::max(stages, 2), 4) : 2;
+  while (ns > 2 && smem_for(ns) > 100 * 1024) --ns;
   const void* kern;
-  if (ns == 2) kern = NB <= 1 ? (const void*)spmm_rbp_kernel<T, VEC, 1, R, EXACT, 2>
-                              : (const void*)spmm_rbp_kernel<T, VEC, 2, R, EXACT, 2>;
-  else kern = NB <= 1 ? (const void*)spmm_rbp_kernel<T, VEC, 1, R, EXACT, R == 4 ? 3 : 2>
-                      : (const void*)spmm_rbp_kernel<T, VEC, 2, R, EXACT, R == 4 ? 3 : 2>;
+#define SBLAS_RBP(NS) (NB <= 1 ? (const void*)spmm_rbp_kernel<T, VEC, 1, R, EXACT, NS> \
+                               : (const void*)spmm_rbp_kernel<T, VEC, 2, R, EXACT, NS>)
+  if (ns == 2) kern = SBLAS_RBP(2);
+  else if (ns == 3) kern = SBLAS_RBP((R == 4 ? 3 : 2));
+  else kern = SBLAS_RBP((R == 4 ? 4 : 2));
+#undef SBLAS_RBP
   const size_t smem = smem_for(ns);
   SBLAS_CHECK(smem <= 200 * 1024, "spmm rowblock pipe: tile needs %zu bytes of shared memory", smem);
   if (smem > 48 * 1024) SBLAS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -619,6 +622,253 @@ static int launch_rbp(cudaStream_t st, const sblasPlan_st* plan, int NB, int log
                       int64_t ldb, const MatSink<T>& sink, int32_t kp) {
   return plan->rb.R == 8 ? launch_rbp_r<T, VEC, EXACT, 8>(st, plan, NB, logP, stages, B, ldb, sink, kp)
                          : launch_rbp_r<T, VEC, EXACT, 4>(st, plan, NB, logP, stages, B, ldb, sink, kp);
+}
+
+// ---- ROWBLOCK, B rows staged per tile (TILEB) -----------------------------------------------------
+// ncu on the kernel above (k = 64, banded): issue slots 55 %, FP64 46 %, LSU wavefronts 61 %, and the
+// rest of the time warps sit in long_scoreboard on the B gathers that miss L1 — every warp fetches
+// "its" B row slices itself although the 8 block rows of a tile share most columns (280 gathers
+// for 63 distinct rows on the 32-wide band).  Here the mirror also carries, per tile of 8 block
+// rows, the ascending list of its DISTINCT columns, and every block the position of its column in
+// that list (spmm_rb.cu, rows with ascending columns only).  The producer warp stages the tile's A
+// blocks AND those B row slices (one cp.async.bulk per distinct column, kp*sizeof(T) bytes) behind
+// the stage's mbarrier, two tiles ahead; the consumer warps take B from shared memory (LDS.128,
+// conflict-free, no global latency in the block loop at all).  Used when the tile's column list
+// fits two stages in ~100 KB (narrow bands, k of one or two slices); else the kernel above.
+template <typename T, int R>
+__host__ __device__ inline size_t rbt_stage_bytes(int32_t cap_blocks, int32_t cap_cols, int NB) {
+  return rbp_stage_bytes<T, R>(cap_blocks) + (size_t)cap_cols * NB * 512;
+}
+
+// tag = colmask.y = presence mask | (position of the block's column in the tile list) << 9, so
+// the byte offset of the staged B row slice is (tag & ~0x1ff) * NB
+template <typename T, int VEC, int NB, int R, bool EXACT, int U, bool TAIL>
+__device__ __forceinline__ void rbt_blocks(uint32_t a_cm, uint32_t a_val, int n, uint32_t a_B,
+                                           typename VecT<T, VEC>::type (&acc)[R][NB]) {
+  using V = typename VecT<T, VEC>::type;
+  constexpr int FULL = (1 << R) - 1;
+  int tag[U];
+  int allmask = FULL;
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    tag[u] = (TAIL && u >= n) ? 0 : lds_i1(a_cm + u * 8 + 4);
+    allmask &= tag[u];
+  }
+  if (!TAIL && allmask == FULL) {
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const uint32_t a_row = a_B + ((uint32_t)tag[u] & ~0x1ffu) * NB;
+      T vv[R];
+      lds_vals<R>(a_val + u * (R * (int)sizeof(T)), vv);
+#pragma unroll
+      for (int nb = 0; nb < NB; ++nb) {
+        const V bv = lds_v(a_row + nb * 512, V());
+#pragma unroll
+        for (int r = 0; r < R; ++r) vmac<EXACT>(vv[r], bv, acc[r][nb]);
+      }
+    }
+  } else {
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if ((tag[u] & kRbMaskBits) == 0) continue;
+      const uint32_t a_row = a_B + ((uint32_t)tag[u] & ~0x1ffu) * NB;
+      T vv[R];
+      lds_vals<R>(a_val + u * (R * (int)sizeof(T)), vv);
+#pragma unroll
+      for (int nb = 0; nb < NB; ++nb) {
+        const V bv = lds_v(a_row + nb * 512, V());
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+          if (tag[u] & (1 << r)) vmac<EXACT>(vv[r], bv, acc[r][nb]);
+      }
+    }
+  }
+}
+
+template <typename T, int VEC, int NB, int R, bool EXACT>
+__global__ void __launch_bounds__(kRbpBlock, 2)
+spmm_rbt_kernel(int64_t n_blockrows, const int32_t* __restrict__ blk_ptr, const int2* __restrict__ colmask,
+                const T* __restrict__ bval, const int32_t* __restrict__ tile_colptr,
+                const int32_t* __restrict__ tile_cols, const T* __restrict__ B, uint32_t ldb_bytes,
+                MatSink<T> sink, int32_t cap_blocks, int32_t cap_cols, int32_t kp) {
+  using V = typename VecT<T, VEC>::type;
+  constexpr int NSTAGE = 2, U = 4, W = kRbpConsumers, ROWB = NB * 512;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw);
+  uint64_t* empty = full + NSTAGE;
+  unsigned char* stages = smem_raw + kRbpHeader;
+  const size_t stage_bytes = rbt_stage_bytes<T, R>(cap_blocks, cap_cols, NB);
+  const uint32_t off_val = (uint32_t)cap_blocks * 8u, off_ptr = off_val + (uint32_t)cap_blocks * (uint32_t)(R * sizeof(T));
+  const uint32_t off_B = off_ptr + 64u;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < NSTAGE; ++s) {
+      mbar_init(&full[s], 32 + 1);
+      mbar_init(&empty[s], kRbpConsumers);
+    }
+    mbar_fence_init();
+  }
+  __syncthreads();
+  const int64_t n_tiles = (n_blockrows + W - 1) / W;
+  const int64_t per_cta = (n_tiles + gridDim.x - 1) / gridDim.x;
+  const int64_t tile0 = (int64_t)blockIdx.x * per_cta;
+  const int my_tiles = (int)max((int64_t)0, min(per_cta, n_tiles - tile0));
+
+  if (warp == kRbpConsumers) {
+    // ---- producer warp --------------------------------------------------------------------------
+    const uint32_t rowb = (uint32_t)kp * (uint32_t)sizeof(T);
+#pragma unroll 1
+    for (int i = 0; i < my_tiles; ++i) {
+      const int s = i % NSTAGE;
+      const int64_t t = tile0 + i;
+      const int64_t br0 = t * W;
+      const int32_t nbr = (int32_t)min((int64_t)W, n_blockrows - br0);
+      const int32_t p0 = __ldg(blk_ptr + br0), p1 = __ldg(blk_ptr + br0 + nbr);
+      const int32_t c0 = __ldg(tile_colptr + t), c1 = __ldg(tile_colptr + t + 1);
+      if (i >= NSTAGE) mbar_wait(&empty[s], (uint32_t)(i / NSTAGE - 1) & 1u);
+      unsigned char* st = stages + (size_t)s * stage_bytes;
+      int2* s_cm = reinterpret_cast<int2*>(st);
+      T* s_val = reinterpret_cast<T*>(st + off_val);
+      int32_t* s_ptr = reinterpret_cast<int32_t*>(st + off_ptr);
+      unsigned char* s_B = st + off_B;
+      const int32_t p0a = p0 & ~1;
+      const int32_t m0 = min((p0 + 1) & ~1, p1);
+      const int32_t m1 = max(p1 & ~1, m0);
+      if (lane == 0) {
+        const uint32_t nb = (uint32_t)(p1 - p0);
+        const uint32_t bytes = (uint32_t)(m1 - m0) * 8u + nb * (uint32_t)(R * sizeof(T)) + (uint32_t)(c1 - c0) * rowb;
+        mbar_arrive_expect_tx(&full[s], bytes);
+        if (m1 > m0) bulk_g2s(s_cm + (m0 - p0a), colmask + m0, (uint32_t)(m1 - m0) * 8u, &full[s]);
+        if (nb) bulk_g2s(s_val + (size_t)(p0 - p0a) * R, bval + (size_t)p0 * R, nb * (uint32_t)(R * sizeof(T)), &full[s]);
+      }
+      __syncwarp();
+      // the tile's distinct B rows, one bulk copy each (after the expect_tx above)
+      for (int32_t j = c0 + lane; j < c1; j += 32) {
+        const int32_t col = __ldg(tile_cols + j);
+        bulk_g2s(s_B + (size_t)(j - c0) * ROWB, reinterpret_cast<const char*>(B) + (uint64_t)(uint32_t)col * ldb_bytes,
+                 rowb, &full[s]);
+      }
+      if (lane == 0 && m0 > p0) cp_async8(s_cm + (p0 - p0a), colmask + p0);
+      if (lane == 1 && p1 > m1) cp_async8(s_cm + (m1 - p0a), colmask + m1);
+      if (lane >= 2 && lane < 2 + nbr + 1) cp_async4(s_ptr + (lane - 2), blk_ptr + br0 + (lane - 2));
+      cp_async_mbar_arrive_noinc(&full[s]);
+    }
+    return;
+  }
+
+  // ---- consumer warps: warp w owns block row w of the tile ----------------------------------------
+  const int w = warp;
+  const int cbase = lane * VEC;
+  bool colok[NB];
+#pragma unroll
+  for (int nb = 0; nb < NB; ++nb) colok[nb] = cbase + nb * 32 * VEC < kp;
+  const uint32_t stages_a = smem_u32(stages);
+  const uint32_t a_C = stages_a + (uint32_t)(NSTAGE * stage_bytes) + (uint32_t)(warp * rbp_cbuf_bytes<R>(NB) + lane * 16);
+
+#pragma unroll 1
+  for (int i = 0; i < my_tiles; ++i) {
+    const int s = i % NSTAGE;
+    const uint32_t st_a = stages_a + (uint32_t)s * (uint32_t)stage_bytes;
+    const int64_t br = (tile0 + i) * W + w;
+    if (br < n_blockrows) {  // old C values first: they do not depend on the stage
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        const int64_t row = br * R + r;
+        if (row < sink.rows) {
+#pragma unroll
+          for (int nb = 0; nb < NB; ++nb)
+            if (colok[nb]) cp_async16_cg(a_C + (uint32_t)((r * NB + nb) * 512), sink.C + row * sink.ldc + cbase + nb * 32 * VEC);
+        }
+      }
+      cp_async_commit();
+    }
+    mbar_wait(&full[s], (uint32_t)(i / NSTAGE) & 1u);
+    if (br < n_blockrows) {
+      const int32_t p0a = lds_i1(st_a + off_ptr) & ~1;
+      const int2 bp = make_int2(lds_i1(st_a + off_ptr + w * 4), lds_i1(st_a + off_ptr + w * 4 + 4));
+      V acc[R][NB];
+#pragma unroll
+      for (int r = 0; r < R; ++r)
+#pragma unroll
+        for (int nb = 0; nb < NB; ++nb) vzero(acc[r][nb]);
+      uint32_t a_cm = st_a + (uint32_t)(bp.x - p0a) * 8u;
+      uint32_t a_val = st_a + off_val + (uint32_t)(bp.x - p0a) * (uint32_t)(R * sizeof(T));
+      const uint32_t a_end = st_a + (uint32_t)(bp.y - p0a) * 8u;
+      const uint32_t a_B = st_a + off_B + (uint32_t)lane * 16u;
+#pragma unroll 1
+      for (; a_cm + U * 8 <= a_end; a_cm += U * 8, a_val += U * R * sizeof(T))
+        rbt_blocks<T, VEC, NB, R, EXACT, U, false>(a_cm, a_val, U, a_B, acc);
+      if (a_cm < a_end)
+        rbt_blocks<T, VEC, NB, R, EXACT, U, true>(a_cm, a_val, (int)(a_end - a_cm) >> 3, a_B, acc);
+      cp_async_wait<0>();
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        const int64_t row = br * R + r;
+        if (row >= sink.rows) break;
+        const int slot = sink.partial_slot((int32_t)row);
+#pragma unroll
+        for (int nb = 0; nb < NB; ++nb) {
+          const int c0 = cbase + nb * 32 * VEC;
+          if (colok[nb]) {
+            if (slot >= 0) {
+              *reinterpret_cast<V*>(sink.carry + (int64_t)slot * sink.kpad + c0) = acc[r][nb];
+            } else {
+              const int64_t off = row * sink.ldc + c0;
+              const V cv = lds_v(a_C + (uint32_t)((r * NB + nb) * 512), V());
+              const V res = vaxpby(sink.alpha, acc[r][nb], sink.beta, cv);
+              *reinterpret_cast<V*>(sink.C + off) = res;
+              for (int d = 0; d < sink.out.n; ++d) *reinterpret_cast<V*>(sink.out.ptr[d] + off) = res;
+            }
+          }
+        }
+      }
+    }
+    fence_proxy_async_smem();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&empty[s]);
+  }
+}
+
+// shared memory of the TILEB kernel for this plan (0: no tile column lists)
+template <typename T>
+static size_t rbt_smem_bytes(const sblasPlan_st* plan, int NB) {
+  const RowBlocks& rb = plan->rb;
+  if (rb.max_tile_cols <= 0 || rb.R != 4) return 0;
+  const int32_t cap_blocks = (rb.max_tile_blocks + 2 + 1) & ~1;
+  return kRbpHeader + 2 * rbt_stage_bytes<T, 4>(cap_blocks, rb.max_tile_cols, NB) +
+         (size_t)kRbpConsumers * rbp_cbuf_bytes<4>(NB);
+}
+
+template <typename T, int VEC, bool EXACT>
+static int launch_rbt(cudaStream_t st, const sblasPlan_st* plan, int NB, const T* B, int64_t ldb,
+                      const MatSink<T>& sink, int32_t kp) {
+  const RowBlocks& rb = plan->rb;
+  constexpr int R = 4;
+  NB = NB <= 1 ? 1 : 2;
+  const int32_t cap_blocks = (rb.max_tile_blocks + 2 + 1) & ~1;
+  const int32_t cap_cols = rb.max_tile_cols;
+  const void* kern = NB == 1 ? (const void*)spmm_rbt_kernel<T, VEC, 1, R, EXACT>
+                             : (const void*)spmm_rbt_kernel<T, VEC, 2, R, EXACT>;
+  const size_t smem = rbt_smem_bytes<T>(plan, NB);
+  SBLAS_CHECK(smem > 0 && smem <= 220 * 1024, "spmm rowblock tileb: tile needs %zu bytes of shared memory", smem);
+  if (smem > 48 * 1024) SBLAS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int per_sm = 0;
+  SBLAS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kRbpBlock, smem));
+  SBLAS_CHECK(per_sm >= 1, "spmm rowblock tileb: kernel does not fit an SM");
+  int n_sm = kNumSM;
+  cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, plan->device);
+  const int64_t n_tiles = ceil_div(rb.n_blockrows, kRbpConsumers);
+  const int grid = (int)std::min<int64_t>(n_tiles, (int64_t)n_sm * per_sm);
+  const int2* cm = (const int2*)rb.d_colmask;
+  const T* bv = (const T*)rb.d_val;
+  const uint32_t ldb_bytes = (uint32_t)(ldb * (int64_t)sizeof(T));
+  void* args[] = {(void*)&rb.n_blockrows, (void*)&rb.d_ptr, (void*)&cm, (void*)&bv, (void*)&rb.d_tile_colptr,
+                  (void*)&rb.d_tile_cols, (void*)&B, (void*)&ldb_bytes, (void*)&sink, (void*)&cap_blocks,
+                  (void*)&cap_cols, (void*)&kp};
+  SBLAS_CUDA(cudaLaunchKernel(kern, dim3(grid), dim3(kRbpBlock), args, smem, st));
+  ++g_launches;
+  return 0;
 }
 
 // ---- COLMAJOR ---------------------------------------------------------------------------------
@@ -773,11 +1023,12 @@ static int spmm_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
     // vectorisable and a row slice keeps at least half a warp busy (k >= 16*VEC); AUTO or SBLAS_SPMM_ROWBLOCK.
     const int want = o ? o->variant : SBLAS_VARIANT_AUTO;
     const bool rb_ok = vec && plan->rb.n_blocks > 0 && plan->rb.is_f64 == (sizeof(T) == 8) && k >= 16 * VF;
-    if ((want == SBLAS_SPMM_ROWBLOCK || want == SBLAS_SPMM_ROWBLOCK_PIPE) && !rb_ok) {
+    if ((want == SBLAS_SPMM_ROWBLOCK || want == SBLAS_SPMM_ROWBLOCK_PIPE || want == SBLAS_SPMM_ROWBLOCK_TILEB) && !rb_ok) {
       set_error("spmm: SBLAS_SPMM_ROWBLOCK needs a plan with row blocks of this value type, 16-byte aligned operands and k >= %d", 16 * VF);
       rc = 2;
     }
-    if (rc == 0 && rb_ok && (want == SBLAS_VARIANT_AUTO || want == SBLAS_SPMM_ROWBLOCK || want == SBLAS_SPMM_ROWBLOCK_PIPE)) {
+    if (rc == 0 && rb_ok && (want == SBLAS_VARIANT_AUTO || want == SBLAS_SPMM_ROWBLOCK || want == SBLAS_SPMM_ROWBLOCK_PIPE ||
+                             want == SBLAS_SPMM_ROWBLOCK_TILEB)) {
       // pipelined flavour: needs the tile statistics and a B pitch below 4 GB.  A pass over A covers
       // P*NB slices of 32*VF columns.  AUTO: P = 1 (tiles of 8 block rows keep the most B rows
       // in L1) and NB = 2 as soon as there are two slices, i.e. k = 256 fp64 takes two passes
@@ -793,6 +1044,15 @@ static int spmm_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
         NBp = n_slices > (1 << logP) ? 2 : 1;
       }
       if (piped && rbp_smem_bytes<T>(plan, NBp, logP) > 100 * 1024) piped = false;  // >= 2 CTAs per SM or not at all
+      // B rows staged once per tile: only on request (SBLAS_SPMM_ROWBLOCK_TILEB).  Measured on b32m
+      // it is level with the pipe kernel (8.6-9.0 ms against 8.9 ms) although its block loop has no
+      // global load left, so AUTO keeps the kernel with the smaller shared-memory footprint.
+      const size_t tb = (piped && logP == 0 && want == SBLAS_SPMM_ROWBLOCK_TILEB) ? rbt_smem_bytes<T>(plan, NBp) : 0;
+      const bool tileb = tb > 0 && tb <= 220u * 1024u;
+      if (want == SBLAS_SPMM_ROWBLOCK_TILEB && !tileb) {
+        set_error("spmm: SBLAS_SPMM_ROWBLOCK_TILEB needs tile column lists (rows with ascending columns, R = 4) that fit shared memory");
+        rc = 2;
+      }
       const int rbpanel = piped ? slice * NBp * (1 << logP) : slice * (plan->rb.R == 8 ? 2 : 4);
       for (int32_t c_off = 0; c_off < k && rc == 0; c_off += rbpanel) {
         const int kp = std::min<int32_t>(rbpanel, k - c_off);
@@ -802,7 +1062,10 @@ static int spmm_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
         ps.k = kp;
         for (int d = 0; d < ps.out.n; ++d) ps.out.ptr[d] = sink.out.ptr[d] + c_off;
         if (ps.carry) ps.carry = sink.carry + c_off;
-        if (piped && kp % VF == 0)
+        if (tileb && kp % VF == 0)
+          rc = exact ? launch_rbt<T, VF, true>(st, plan, NBp, B + c_off, ldb, ps, kp)
+                     : launch_rbt<T, VF, false>(st, plan, NBp, B + c_off, ldb, ps, kp);
+        else if (piped && kp % VF == 0)
           rc = exact ? launch_rbp<T, VF, true>(st, plan, NBp, logP, o ? o->stages : 0, B + c_off, ldb, ps, kp)
                      : launch_rbp<T, VF, false>(st, plan, NBp, logP, o ? o->stages : 0, B + c_off, ldb, ps, kp);
         else

@@ -73,6 +73,102 @@ __global__ void rb_tile_max_kernel(const int32_t* __restrict__ blk_ptr, int64_t 
   if ((threadIdx.x & 31) == 0) atomicMax(out, v);
 }
 
+// distinct columns of every tile of W = 8 block rows: 8-way merge of the block rows' (ascending)
+// column lists.  Pass 1 (FILL = false) counts and checks that every block row IS ascending
+// (*unsorted is raised otherwise); pass 2 writes the list and tags every block with its position.
+template <bool FILL>
+__global__ void __launch_bounds__(128)
+rb_tile_cols_kernel(int64_t n_blockrows, const int32_t* __restrict__ blk_ptr, int2* __restrict__ colmask,
+                    int32_t* __restrict__ counts, const int32_t* __restrict__ colptr,
+                    int32_t* __restrict__ tile_cols, int32_t* __restrict__ unsorted) {
+  constexpr int W = 8;
+  const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  const int64_t n_tiles = (n_blockrows + W - 1) / W;
+  if (t >= n_tiles) return;
+  int32_t p[W], e[W], head[W];
+#pragma unroll
+  for (int j = 0; j < W; ++j) {
+    const int64_t br = t * W + j;
+    p[j] = br < n_blockrows ? blk_ptr[br] : 0;
+    e[j] = br < n_blockrows ? blk_ptr[br + 1] : 0;
+    head[j] = p[j] < e[j] ? colmask[p[j]].x : INT32_MAX;
+  }
+  int32_t n = 0;
+  bool bad = false;
+  const int64_t out = FILL ? colptr[t] : 0;
+  while (true) {
+    int32_t c = head[0];
+#pragma unroll
+    for (int j = 1; j < W; ++j) c = min(c, head[j]);
+    if (c == INT32_MAX) break;
+#pragma unroll
+    for (int j = 0; j < W; ++j) {
+      if (head[j] == c) {
+        if (FILL) colmask[p[j]].y = (colmask[p[j]].y & kRbMaskBits) | (n << 9);
+        ++p[j];
+        const int32_t nh = p[j] < e[j] ? colmask[p[j]].x : INT32_MAX;
+        bad = bad || nh <= c;
+        head[j] = nh;
+      }
+    }
+    if (FILL) tile_cols[out + n] = c;
+    ++n;
+    if (bad) break;
+  }
+  if (!FILL) {
+    counts[t] = n;
+    if (bad) atomicExch(unsorted, 1);
+  }
+}
+
+// builds rb.d_tile_colptr / d_tile_cols / max_tile_cols (left empty when some row is not ascending)
+static int build_tile_cols(cudaStream_t st, RowBlocks& rb) {
+  const int64_t n_tiles = ceil_div(rb.n_blockrows, 8);
+  int32_t* counts = nullptr;
+  SBLAS_CUDA(cudaMalloc(&counts, sizeof(int32_t) * (size_t)(n_tiles + 2)));
+  SBLAS_CUDA(cudaMemsetAsync(counts, 0, sizeof(int32_t) * (size_t)(n_tiles + 2), st));
+  int32_t* flag = counts + n_tiles + 1;
+  const int grid = (int)ceil_div(n_tiles, 128);
+  rb_tile_cols_kernel<false><<<grid, 128, 0, st>>>(rb.n_blockrows, rb.d_ptr, (int2*)rb.d_colmask, counts, nullptr,
+                                                   nullptr, flag);
+  SBLAS_LAUNCH_CHECK();
+  int32_t unsorted = 0;
+  SBLAS_CUDA(cudaMemcpyAsync(&unsorted, flag, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+  SBLAS_CUDA(cudaStreamSynchronize(st));
+  if (unsorted) {
+    SBLAS_CUDA(cudaFree(counts));
+    return 0;
+  }
+  SBLAS_CUDA(cudaMalloc(&rb.d_tile_colptr, sizeof(int32_t) * (size_t)(n_tiles + 1)));
+  void* tmp = nullptr;
+  size_t tb = 0;
+  SBLAS_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tb, counts, rb.d_tile_colptr, (int)(n_tiles + 1), st));
+  SBLAS_CUDA(cudaMalloc(&tmp, tb));
+  SBLAS_CUDA(cub::DeviceScan::ExclusiveSum(tmp, tb, counts, rb.d_tile_colptr, (int)(n_tiles + 1), st));
+  void* mx = nullptr;
+  size_t mb = 0;
+  int32_t* d_max = nullptr;
+  SBLAS_CUDA(cudaMalloc(&d_max, sizeof(int32_t)));
+  SBLAS_CUDA(cub::DeviceReduce::Max(nullptr, mb, counts, d_max, (int)n_tiles, st));
+  SBLAS_CUDA(cudaMalloc(&mx, mb));
+  SBLAS_CUDA(cub::DeviceReduce::Max(mx, mb, counts, d_max, (int)n_tiles, st));
+  int32_t total = 0, max_cols = 0;
+  SBLAS_CUDA(cudaMemcpyAsync(&total, rb.d_tile_colptr + n_tiles, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+  SBLAS_CUDA(cudaMemcpyAsync(&max_cols, d_max, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+  SBLAS_CUDA(cudaStreamSynchronize(st));
+  SBLAS_CUDA(cudaFree(tmp));
+  SBLAS_CUDA(cudaFree(mx));
+  SBLAS_CUDA(cudaFree(d_max));
+  SBLAS_CUDA(cudaMalloc(&rb.d_tile_cols, sizeof(int32_t) * (size_t)std::max(total, 1)));
+  rb_tile_cols_kernel<true><<<grid, 128, 0, st>>>(rb.n_blockrows, rb.d_ptr, (int2*)rb.d_colmask, nullptr,
+                                                  rb.d_tile_colptr, rb.d_tile_cols, nullptr);
+  SBLAS_LAUNCH_CHECK();
+  SBLAS_CUDA(cudaStreamSynchronize(st));
+  SBLAS_CUDA(cudaFree(counts));
+  rb.max_tile_cols = max_cols;
+  return 0;
+}
+
 template <typename T, int R>
 static int build_rowblocks(cudaStream_t st, sblasPlan_st* plan, const int32_t* ci, const T* val, bool force,
                            double min_fill) {
@@ -126,7 +222,7 @@ static int build_rowblocks(cudaStream_t st, sblasPlan_st* plan, const int32_t* c
   rb.max_tile_blocks4 = tile_max[1];
   rb.max_tile_blocks2 = tile_max[2];
   SBLAS_CUDA(cudaFree(counts));
-  return 0;
+  return build_tile_cols(st, rb);
 }
 
 // R = 0 (what sync2gpu asks for): R = 4, kept when its fill reaches kRowBlockMinFill.  R = 4 / 8:
@@ -151,6 +247,8 @@ void rowblocks_free(sblasPlan_st* plan) {
   if (rb.d_ptr) cudaFree(rb.d_ptr);
   if (rb.d_colmask) cudaFree(rb.d_colmask);
   if (rb.d_val) cudaFree(rb.d_val);
+  if (rb.d_tile_colptr) cudaFree(rb.d_tile_colptr);
+  if (rb.d_tile_cols) cudaFree(rb.d_tile_cols);
   rb = RowBlocks();
 }
 

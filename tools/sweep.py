@@ -26,7 +26,7 @@ def main():
     ap.add_argument("--grid", default="default")
     ap.add_argument("--out", default=None)
     ap.add_argument("--dirty-flush", action="store_true")
-    ap.add_argument("--only", type=int, default=None, help="only this variant")
+    ap.add_argument("--only", default=None, help="only these variants (comma-separated numbers)")
     ap.add_argument("--rb", type=int, default=0, help="row-block height of the SpMM mirror (0 = auto, 4, 8)")
     args = ap.parse_args()
     import torch
@@ -62,10 +62,11 @@ def main():
                 for l in ((0,) if args.grid == "default" else (0, 32))]
     if wl['op'] == 'spmm':
         print('rowblocks', plan.build_rowblocks(ci, v, R=args.rb), flush=True)
-        grid = [dict(variant=pkg.SPMM_ROWBLOCK_PIPE, flags=f, stages=st, lanes=P) for f in (0, 1) for st in (2,) for P in (1, 2, 4)] + [dict(variant=pkg.SPMM_ROWBLOCK, flags=f) for f in (0, 1)] + [dict(variant=pkg.SPMM_ROWMAJOR, tile=t, flags=f) for t in (512, 2048) for f in (0, 1)]
+        grid = [dict(variant=pkg.SPMM_ROWBLOCK_PIPE, flags=f, stages=st, lanes=P) for f in (0, 1) for st in (2,) for P in (1,)] + [dict(variant=pkg.SPMM_ROWBLOCK_TILEB, flags=f) for f in (0, 1)] + [dict(variant=pkg.SPMM_ROWBLOCK, flags=f) for f in (0, 1)] + [dict(variant=pkg.SPMM_ROWMAJOR, tile=t, flags=f) for t in (512, 2048) for f in (0, 1)]
     res = []
     if args.only is not None:
-        grid = [g for g in grid if g.get('variant') == args.only]
+        keep = {int(x) for x in str(args.only).split(",")}
+        grid = [g for g in grid if g.get('variant') in keep]
     for g in grid:
         o = pkg.make_opts(**g)
 
