@@ -75,7 +75,9 @@ enum {
   SBLAS_FLAG_PREFETCH_B = 16,  /* SBLAS_SPMM_ROWBLOCK_PIPE: the producer warp prefetches the B rows of
                                   the tile it just staged into L1; AUTO sets it for one-slice panels
                                   (k <= 64 fp64 / 128 fp32), where it measured 5% faster */
-  SBLAS_FLAG_NO_PREFETCH_B = 32 /* ... never */
+  SBLAS_FLAG_NO_PREFETCH_B = 32, /* ... never */
+  SBLAS_FLAG_SPLIT_LEGACY = 64  /* SBLAS_SPMV_SPLIT: the first phase-2 (sub-warp per row from shared memory)
+                                   instead of the balanced merge-path walk; kept for A/B measurements */
 };
 enum { SBLAS_ROW_MAJOR = 0, SBLAS_COL_MAJOR = 1 }; /* = MajorOrder, matrix.h:37 */
 

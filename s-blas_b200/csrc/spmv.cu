@@ -605,6 +605,99 @@ spmv_split_kernel(const int32_t* __restrict__ split_row, int32_t T_items, int32_
   reduce_rows_dispatch<T, BLOCK>(lanes_for_avg((jb - ja) / nloc), s_prod, s_rp, nloc, ja & ~3, ss);
 }
 
+// SPLIT, balanced flavour (the default): same merge-path tiles, same carry / head tables and fix-up
+// kernel, but phase 2 is ALSO a merge-path walk — thread t owns the merge items [t*I, (t+1)*I) of the
+// tile (I = ceil(T_items / BLOCK) row ends or products, found by a binary search over the tile's
+// clamped row pointers in shared memory) and sums its products in CSR order.  Rows that lie inside
+// one thread are emitted directly; a row's last piece takes the partial sums of the threads before
+// it from a CTA-wide SEGMENTED scan of the per-thread trailing sums (warp shuffles, then the eight
+// warp totals), so a tile that is one slice of a 150 000-nnz row costs the same as a tile of 1 500
+// short rows.  The old phase 2 gave such a tile to ONE sub-warp while seven warps sat at the barrier
+// (ncu, config 4: `barrier` + `short_scoreboard` + `mio_throttle` > `long_scoreboard`).
+// Summation order: CSR order inside a thread, tree order across threads (deterministic).
+template <typename T, int BLOCK, bool VEC>
+__global__ void __launch_bounds__(BLOCK)
+spmv_merge_kernel(const int32_t* __restrict__ split_row, int32_t T_items, int32_t rows, int64_t nnz,
+                  const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colidx,
+                  const T* __restrict__ val, const T* __restrict__ x, RowSink<T> sink,
+                  T* carry_out, T* head_val, int32_t* head_row, int32_t cap_nnz) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ T s_wv[BLOCK / 32];
+  __shared__ int s_wf[BLOCK / 32];
+  T* s_prod = reinterpret_cast<T*>(smem_raw);
+  int32_t* s_rp = reinterpret_cast<int32_t*>(s_prod + cap_nnz);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int b = blockIdx.x;
+  const int32_t ra = split_row[b], rb = split_row[b + 1];
+  int64_t da = (int64_t)b * T_items, db = da + T_items;
+  if (db > rows + nnz) db = rows + nnz;
+  const int32_t ja = (int32_t)(da - ra), jb = (int32_t)(db - rb);
+  const int32_t nfin = rb - ra;  // rows whose end lies in this tile
+  // s_rp[i + 1] - ja = local nnz count at which row ra + i ends (i < nfin); clamped like the old kernel
+  for (int i = tid; i <= nfin; i += BLOCK) {
+    int32_t v = rowptr[ra + i];
+    s_rp[i] = v < ja ? ja : (v > jb ? jb : v);
+  }
+  __syncthreads();
+  const bool head_open = nfin > 0 && rowptr[ra] < ja;
+  if (tid == 0) head_row[b] = head_open ? ra : -1;
+  stage_products<T, BLOCK, VEC>(colidx, val, x, ja, jb, s_prod);
+  __syncthreads();
+
+  const int32_t Nl = jb - ja, total = nfin + Nl;
+  const int32_t off = ja - (ja & ~3);  // products are parked at s_prod[j - (ja & ~3)]
+  const int32_t items = (T_items + BLOCK - 1) / BLOCK;
+  const int32_t d0 = min(tid * items, total), d1 = min(d0 + items, total);
+  int lo = max(0, d0 - Nl), hi = min(d0, nfin);
+  while (lo < hi) {  // row end `mid` comes before diagonal d0 iff all its nnz do (split_search_kernel's rule)
+    const int mid = (lo + hi) >> 1;
+    if (s_rp[mid + 1] - ja <= d0 - mid - 1) lo = mid + 1; else hi = mid;
+  }
+  int i = lo, j = d0 - lo;
+  int e = i < nfin ? s_rp[i + 1] - ja : 0x7fffffff;
+  T sum = 0, first_val = 0;
+  int first_row = -1;
+  for (int d = d0; d < d1; ++d) {
+    if (j >= e) {  // row end: rows begun in this thread go out at once, the first one waits for its carry-in
+      if (first_row < 0) { first_row = i; first_val = sum; }
+      else sink.put(ra + i, sum);
+      sum = 0;
+      ++i;
+      e = i < nfin ? s_rp[i + 1] - ja : 0x7fffffff;
+    } else {
+      sum = add_rn(sum, s_prod[off + j]);
+      ++j;
+    }
+  }
+  // segmented inclusive scan of (has_row_end, trailing sum): (f1,v1) (+) (f2,v2) = (f1|f2, f2 ? v2 : v1+v2)
+  int f = first_row >= 0;
+  T v = sum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const T pv = __shfl_up_sync(0xffffffffu, v, o);
+    const int pf = __shfl_up_sync(0xffffffffu, f, o);
+    if (lane >= o) {
+      if (!f) v = add_rn(pv, v);
+      f |= pf;
+    }
+  }
+  T ev = __shfl_up_sync(0xffffffffu, v, 1);
+  int ef = __shfl_up_sync(0xffffffffu, f, 1);
+  if (lane == 0) { ev = 0; ef = 0; }
+  if (lane == 31) { s_wv[warp] = v; s_wf[warp] = f; }
+  __syncthreads();
+  T pv = 0;
+  for (int w = 0; w < warp; ++w) pv = s_wf[w] ? s_wv[w] : add_rn(pv, s_wv[w]);
+  if (first_row >= 0) {
+    const T carry_in = ef ? ev : add_rn(pv, ev);
+    const T res = add_rn(carry_in, first_val);
+    if (first_row == 0 && head_open) head_val[b] = res;  // begun in an earlier tile -> fix-up kernel
+    else sink.put(ra + first_row, res);
+  }
+  if (tid == BLOCK - 1)  // what is left after the tile's last row end belongs to the cut row rb
+    carry_out[b] = rb < rows ? (f ? v : add_rn(pv, v)) : T(0);
+}
+
 template <typename T>
 __global__ void spmv_split_fixup_kernel(const int32_t* __restrict__ rowptr, int32_t T_items,
                                         int32_t n_tiles, const T* __restrict__ carry_out,
@@ -826,7 +919,9 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
       } else {
         const int32_t cap = (tile + 9) & ~3;
         const int smem = cap * (int)sizeof(T) + (tile + 3) * (int)sizeof(int32_t);
-        auto kern = vec ? spmv_split_kernel<T, kSpmvBlock, true> : spmv_split_kernel<T, kSpmvBlock, false>;
+        const bool legacy = (flags & SBLAS_FLAG_SPLIT_LEGACY) != 0;  // old phase 2 (sub-warp per row), for A/B runs
+        auto kern = legacy ? (vec ? spmv_split_kernel<T, kSpmvBlock, true> : spmv_split_kernel<T, kSpmvBlock, false>)
+                           : (vec ? spmv_merge_kernel<T, kSpmvBlock, true> : spmv_merge_kernel<T, kSpmvBlock, false>);
         if ((rc = set_smem_once<T>((const void*)kern, smem)) == 0) {
           kern<<<tt->n_tiles, kSpmvBlock, smem, st>>>(tt->d_tile_row, tile, rows, nnz, rp, ci, v, x,
                                                       sink, carry_out, head_val, head_row, cap);

@@ -1,0 +1,9 @@
+#!/bin/bash
+# state check of HEAD: full GPU parity suite, smoke, both bench arms
+mkdir -p gpurun_out
+timeout 1500 python -m pytest tests -m gpu -q -x --timeout=300 -p no:cacheprovider > gpurun_out/pytest_gpu.log 2>&1
+echo "pytest gpu exit $?"; tail -3 gpurun_out/pytest_gpu.log
+timeout 300 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > gpurun_out/smoke.log 2>&1; echo "smoke $?"; tail -2 gpurun_out/smoke.log
+timeout 600 python bench.py > gpurun_out/bench_c2.json 2> gpurun_out/bench_c2.err; echo "bench $?"; tail -1 gpurun_out/bench_c2.json
+timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "ref $?"; tail -1 gpurun_out/bench_ref.json
+echo finished
