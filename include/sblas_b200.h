@@ -76,8 +76,13 @@ enum {
                                   the tile it just staged into L1; AUTO sets it for one-slice panels
                                   (k <= 64 fp64 / 128 fp32), where it measured 5% faster */
   SBLAS_FLAG_NO_PREFETCH_B = 32, /* ... never */
-  SBLAS_FLAG_SPLIT_LEGACY = 64  /* SBLAS_SPMV_SPLIT: the first phase-2 (sub-warp per row from shared memory)
-                                   instead of the balanced merge-path walk; kept for A/B measurements */
+  SBLAS_FLAG_SPLIT_SERIAL = 128, /* SBLAS_SPMV_SPLIT: row pointers loaded before the A stream and y read in the
+                                   epilogue (the first version; four dependent memory round trips per CTA) */
+  SBLAS_FLAG_SPLIT_SEG = 256,   /* SBLAS_SPMV_SPLIT: phase 2 as an in-place segmented sum (row-start bitmap,
+                                   reverse segmented scan of the thread leads), balanced for any row mix */
+  SBLAS_FLAG_SPLIT_MERGE = 64   /* SBLAS_SPMV_SPLIT: balanced merge-path walk in phase 2 (every thread owns
+                                   tile/256 merge items, CTA-wide segmented scan of the carries) instead of a
+                                   sub-warp per row; measured slower on config 4 (0.73 against 0.66 ms), opt-in */
 };
 enum { SBLAS_ROW_MAJOR = 0, SBLAS_COL_MAJOR = 1 }; /* = MajorOrder, matrix.h:37 */
 

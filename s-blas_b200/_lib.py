@@ -14,7 +14,9 @@ VARIANT_AUTO, SPMV_TILE, SPMV_VECTOR, SPMV_SPLIT, SPMV_PIPE = 0, 1, 2, 3, 4
 SPMM_ROWMAJOR, SPMM_COLMAJOR, SPMM_ROWBLOCK, SPMM_ROWBLOCK_PIPE, SPMM_ROWBLOCK_TILEB = 1, 2, 3, 4, 5
 FLAG_FMA, FLAG_HEAD_PARTIAL, FLAG_TAIL_PARTIAL, FLAG_NO_L1 = 1, 2, 4, 8
 FLAG_PREFETCH_B, FLAG_NO_PREFETCH_B = 16, 32
-FLAG_SPLIT_LEGACY = 64
+FLAG_SPLIT_MERGE = 64
+FLAG_SPLIT_SERIAL = 128
+FLAG_SPLIT_SEG = 256
 ROW_MAJOR, COL_MAJOR = 0, 1
 
 

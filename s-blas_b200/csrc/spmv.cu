@@ -161,11 +161,14 @@ struct TileSink {
 };
 
 // Phase 1 shared by TILE and SPLIT: products of nnz [n0, n1) -> s_prod[j - (n0 & ~3)].
-template <typename T, int BLOCK, bool VEC>
+// NOL1: gather x past L1 (ld.global.nc.L1::no_allocate) — an in-flight gather that allocates holds an L1
+// line, and with most of the 256 KB carved out as shared memory the lines cap the gathers in flight.
+template <typename T, int BLOCK, bool VEC, bool NOL1 = false>
 __device__ __forceinline__ void stage_products(const int32_t* __restrict__ colidx,
                                                const T* __restrict__ val,
                                                const T* __restrict__ x, int32_t n0, int32_t n1,
                                                T* s_prod) {
+  auto gx = [&](int32_t c) -> T { return NOL1 ? ldg_stream(x + c) : __ldg(x + c); };
   const int tid = threadIdx.x;
   const int32_t n0a = n0 & ~3;
   if (VEC) {
@@ -178,15 +181,15 @@ __device__ __forceinline__ void stage_products(const int32_t* __restrict__ colid
         const int4 c = ldg_stream_i4(reinterpret_cast<const int4*>(colidx) + g);
         T v[4];
         load4_stream(val, g, v);
-        p[0] = mul_rn(v[0], __ldg(x + c.x));
-        p[1] = mul_rn(v[1], __ldg(x + c.y));
-        p[2] = mul_rn(v[2], __ldg(x + c.z));
-        p[3] = mul_rn(v[3], __ldg(x + c.w));
+        p[0] = mul_rn(v[0], gx(c.x));
+        p[1] = mul_rn(v[1], gx(c.y));
+        p[2] = mul_rn(v[2], gx(c.z));
+        p[3] = mul_rn(v[3], gx(c.w));
       } else {
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
           const int j = base + e;
-          p[e] = (j >= n0 && j < n1) ? mul_rn(ldg_stream(val + j), __ldg(x + ldg_stream(colidx + j)))
+          p[e] = (j >= n0 && j < n1) ? mul_rn(ldg_stream(val + j), gx(ldg_stream(colidx + j)))
                                      : T(0);
         }
       }
@@ -195,7 +198,7 @@ __device__ __forceinline__ void stage_products(const int32_t* __restrict__ colid
   } else {
 #pragma unroll 4
     for (int j = n0 + tid; j < n1; j += BLOCK)
-      s_prod[j - n0a] = mul_rn(ldg_stream(val + j), __ldg(x + ldg_stream(colidx + j)));
+      s_prod[j - n0a] = mul_rn(ldg_stream(val + j), gx(ldg_stream(colidx + j)));
   }
 }
 
@@ -571,7 +574,10 @@ struct SplitSink {
   }
 };
 
-template <typename T, int BLOCK, bool VEC>
+// OVL: the tile's nnz window [ja, jb) follows from the split table alone, so the row pointers are
+// fetched by LDGSTS (raw, clamped when read) and the old y rows are prefetched into L2 WHILE the A
+// stream and the x gathers are in flight — two dependent DRAM round trips instead of four per CTA.
+template <typename T, int BLOCK, bool VEC, bool OVL, bool NOL1 = false>
 __global__ void __launch_bounds__(BLOCK)
 spmv_split_kernel(const int32_t* __restrict__ split_row, int32_t T_items, int32_t rows, int64_t nnz,
                   const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colidx,
@@ -587,33 +593,50 @@ spmv_split_kernel(const int32_t* __restrict__ split_row, int32_t T_items, int32_
   if (db > rows + nnz) db = rows + nnz;
   const int32_t ja = (int32_t)(da - ra), jb = (int32_t)(db - rb);
   const int32_t nfin = rb - ra;  // rows whose end lies in this tile
-  // local row pointers clamped to the tile's nnz window; entry nfin+1 closes the cut row rb
-  for (int i = tid; i <= nfin; i += BLOCK) {
-    int32_t v = rowptr[ra + i];
-    s_rp[i] = v < ja ? ja : (v > jb ? jb : v);
-  }
-  if (tid == 0) s_rp[nfin + 1] = jb;
-  __syncthreads();
-  const bool head_open = nfin > 0 && rowptr[ra] < ja;
-  if (tid == 0) head_row[b] = head_open ? ra : -1;
-  stage_products<T, BLOCK, VEC>(colidx, val, x, ja, jb, s_prod);
-  __syncthreads();
   const int nloc = rb < rows ? nfin + 1 : nfin;  // + the cut row, if there is one
+  bool head_open;
+  if (OVL) {
+    for (int i = tid; i <= nfin; i += BLOCK) cp_async4(&s_rp[i], &rowptr[ra + i]);
+    cp_async_commit();
+    if (tid == 0) s_rp[nfin + 1] = jb;  // closes the cut row rb
+    constexpr int kPer = 32 / (int)sizeof(T);  // one prefetch per 32-byte sector of y
+    for (int i = tid * kPer; i < nfin; i += BLOCK * kPer) prefetch_l2(sink.y + ra + i);
+    stage_products<T, BLOCK, VEC, NOL1>(colidx, val, x, ja, jb, s_prod);
+    cp_async_wait<0>();
+    __syncthreads();
+    head_open = nfin > 0 && s_rp[0] < ja;
+  } else {
+    // local row pointers clamped to the tile's nnz window; entry nfin+1 closes the cut row rb
+    for (int i = tid; i <= nfin; i += BLOCK) {
+      int32_t v = rowptr[ra + i];
+      s_rp[i] = v < ja ? ja : (v > jb ? jb : v);
+    }
+    if (tid == 0) s_rp[nfin + 1] = jb;
+    __syncthreads();
+    head_open = nfin > 0 && rowptr[ra] < ja;
+    stage_products<T, BLOCK, VEC>(colidx, val, x, ja, jb, s_prod);
+    __syncthreads();
+  }
+  if (tid == 0) head_row[b] = head_open ? ra : -1;
   if (rb >= rows && tid == 0) carry_out[b] = T(0);
   if (nloc <= 0) return;
   const SplitSink<T> ss{sink, ra, rb < rows ? nfin : -1, head_open, carry_out + b, head_val + b};
-  reduce_rows_dispatch<T, BLOCK>(lanes_for_avg((jb - ja) / nloc), s_prod, s_rp, nloc, ja & ~3, ss);
+  if (OVL)
+    reduce_rows_clamped_dispatch<T, BLOCK>(lanes_for_avg((jb - ja) / nloc), s_prod, s_rp, nloc, ja & ~3, ja, jb, ss);
+  else
+    reduce_rows_dispatch<T, BLOCK>(lanes_for_avg((jb - ja) / nloc), s_prod, s_rp, nloc, ja & ~3, ss);
 }
 
-// SPLIT, balanced flavour (the default): same merge-path tiles, same carry / head tables and fix-up
+// SPLIT, balanced flavour (SBLAS_FLAG_SPLIT_MERGE): same merge-path tiles, same carry / head tables and fix-up
 // kernel, but phase 2 is ALSO a merge-path walk — thread t owns the merge items [t*I, (t+1)*I) of the
 // tile (I = ceil(T_items / BLOCK) row ends or products, found by a binary search over the tile's
 // clamped row pointers in shared memory) and sums its products in CSR order.  Rows that lie inside
 // one thread are emitted directly; a row's last piece takes the partial sums of the threads before
 // it from a CTA-wide SEGMENTED scan of the per-thread trailing sums (warp shuffles, then the eight
 // warp totals), so a tile that is one slice of a 150 000-nnz row costs the same as a tile of 1 500
-// short rows.  The old phase 2 gave such a tile to ONE sub-warp while seven warps sat at the barrier
-// (ncu, config 4: `barrier` + `short_scoreboard` + `mio_throttle` > `long_scoreboard`).
+// short rows (the default phase 2 gives such a tile to ONE sub-warp while seven warps sit at the
+// barrier).  Measured on config 4 (profiles/r01_sweep_c4_merge.log): 0.73 ms against 0.66 ms for the
+// default at tile 1536 — the imbalance was not the bound, the divergent x gathers are — so opt-in only.
 // Summation order: CSR order inside a thread, tree order across threads (deterministic).
 template <typename T, int BLOCK, bool VEC>
 __global__ void __launch_bounds__(BLOCK)
@@ -696,6 +719,107 @@ spmv_merge_kernel(const int32_t* __restrict__ split_row, int32_t T_items, int32_
   }
   if (tid == BLOCK - 1)  // what is left after the tile's last row end belongs to the cut row rb
     carry_out[b] = rb < rows ? (f ? v : add_rn(pv, v)) : T(0);
+}
+
+// SPLIT, segmented-sum flavour: phase 2 without a search and without global accesses in its loop.
+//   (a) every non-empty row of the tile sets one bit (its first product) in a shared bitmap;
+//   (b) thread t walks its I = ceil(T_items / BLOCK) consecutive products once, closing a segment
+//       at every set bit: finished segments are written IN PLACE over the segment's first
+//       product, the products before its first bit (`lead`) belong to a head in an earlier
+//       thread, the last segment stays open;
+//   (c) a reverse segmented scan over the threads' (has_bit, lead) pairs (warp shuffles + the eight
+//       warp totals) hands every open segment the leads of the threads after it;
+//   (d) one coalesced pass over the rows reads each row's sum from its first product slot and does
+//       the fused y update.
+// Balanced for any row-length mix (a tile that is one slice of a 150 000-nnz row costs the same as a
+// tile of short rows), ~100 instructions per thread against ~250 for the sub-warp-per-row phase 2.
+template <typename T, int BLOCK, bool VEC>
+__global__ void __launch_bounds__(BLOCK)
+spmv_split_seg_kernel(const int32_t* __restrict__ split_row, int32_t T_items, int32_t rows, int64_t nnz,
+                      const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colidx,
+                      const T* __restrict__ val, const T* __restrict__ x, RowSink<T> sink,
+                      T* carry_out, T* head_val, int32_t* head_row, int32_t cap_nnz) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ T s_wv[BLOCK / 32];
+  __shared__ int s_wf[BLOCK / 32];
+  T* s_prod = reinterpret_cast<T*>(smem_raw);
+  int32_t* s_rp = reinterpret_cast<int32_t*>(s_prod + cap_nnz);
+  uint32_t* s_flag = reinterpret_cast<uint32_t*>(s_rp + T_items + 3);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int b = blockIdx.x;
+  const int32_t ra = split_row[b], rb = split_row[b + 1];
+  int64_t da = (int64_t)b * T_items, db = da + T_items;
+  if (db > rows + nnz) db = rows + nnz;
+  const int32_t ja = (int32_t)(da - ra), jb = (int32_t)(db - rb);
+  const int32_t nfin = rb - ra;
+  const int nloc = rb < rows ? nfin + 1 : nfin;
+  for (int i = tid; i <= nfin; i += BLOCK) cp_async4(&s_rp[i], &rowptr[ra + i]);
+  cp_async_commit();
+  if (tid == 0) s_rp[nfin + 1] = jb;
+  for (int i = tid; i < (T_items + 31) / 32 + 1; i += BLOCK) s_flag[i] = 0u;
+  constexpr int kPer = 32 / (int)sizeof(T);
+  for (int i = tid * kPer; i < nfin; i += BLOCK * kPer) prefetch_l2(sink.y + ra + i);
+  stage_products<T, BLOCK, VEC>(colidx, val, x, ja, jb, s_prod);
+  cp_async_wait<0>();
+  __syncthreads();
+  const bool head_open = nfin > 0 && s_rp[0] < ja;
+  if (tid == 0) head_row[b] = head_open ? ra : -1;
+  if (rb >= rows && tid == 0) carry_out[b] = T(0);
+  if (nloc <= 0) return;  // block-uniform
+  // (a) one bit per non-empty row, at its first product (row pointers clamped to the tile's window)
+  for (int i = tid; i < nloc; i += BLOCK) {
+    const int s = min(max(s_rp[i], ja), jb) - ja, e = min(max(s_rp[i + 1], ja), jb) - ja;
+    if (e > s) atomicOr(&s_flag[s >> 5], 1u << (s & 31));
+  }
+  __syncthreads();
+  // (b)
+  const int32_t Nl = jb - ja, off = ja - (ja & ~3);
+  const int32_t items = (T_items + BLOCK - 1) / BLOCK;
+  const int p0 = min(tid * items, Nl), p1 = min(p0 + items, Nl);
+  T lead = 0, cur = 0;
+  int head = -1;
+  for (int p = p0; p < p1; ++p) {
+    const bool fl = (s_flag[p >> 5] >> (p & 31)) & 1u;
+    const T pr = s_prod[off + p];
+    if (fl) {
+      if (head >= 0) s_prod[off + head] = cur; else lead = cur;
+      head = p;
+      cur = pr;
+    } else {
+      cur = add_rn(cur, pr);
+    }
+  }
+  if (head < 0) lead = cur;
+  // (c) R_t = lead_t + (has_bit_t ? 0 : R_{t+1}); the open segment of thread t takes R_{t+1}
+  int f = head >= 0;
+  T v = lead;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const T nv = __shfl_down_sync(0xffffffffu, v, o);
+    const int nf = __shfl_down_sync(0xffffffffu, f, o);
+    if (lane + o < 32) {
+      if (!f) v = add_rn(v, nv);
+      f |= nf;
+    }
+  }
+  T nvx = __shfl_down_sync(0xffffffffu, v, 1);
+  int nfx = __shfl_down_sync(0xffffffffu, f, 1);
+  if (lane == 31) { nvx = 0; nfx = 0; }
+  if (lane == 0) { s_wv[warp] = v; s_wf[warp] = f; }
+  __syncthreads();
+  if (head >= 0) {
+    T X = 0;  // suffix over the warps after this one
+    for (int w = BLOCK / 32 - 1; w > warp; --w) X = s_wf[w] ? s_wv[w] : add_rn(s_wv[w], X);
+    const T rest = nfx ? nvx : add_rn(nvx, X);
+    s_prod[off + head] = add_rn(cur, rest);
+  }
+  __syncthreads();
+  // (d)
+  const SplitSink<T> ss{sink, ra, rb < rows ? nfin : -1, head_open, carry_out + b, head_val + b};
+  for (int i = tid; i < nloc; i += BLOCK) {
+    const int s = min(max(s_rp[i], ja), jb) - ja, e = min(max(s_rp[i + 1], ja), jb) - ja;
+    ss.put(i, e > s ? s_prod[off + s] : T(0));
+  }
 }
 
 template <typename T>
@@ -918,10 +1042,18 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
         }
       } else {
         const int32_t cap = (tile + 9) & ~3;
-        const int smem = cap * (int)sizeof(T) + (tile + 3) * (int)sizeof(int32_t);
-        const bool legacy = (flags & SBLAS_FLAG_SPLIT_LEGACY) != 0;  // old phase 2 (sub-warp per row), for A/B runs
-        auto kern = legacy ? (vec ? spmv_split_kernel<T, kSpmvBlock, true> : spmv_split_kernel<T, kSpmvBlock, false>)
+        const int smem = cap * (int)sizeof(T) + (tile + 3) * (int)sizeof(int32_t) + ((tile + 31) / 32 + 2) * 4;
+        // phase 2: sub-warp per row (default) or the balanced merge-path walk (opt-in: it removes the idle
+        // warps on tiles that are one slice of a long row, but its search + scan cost more than they did)
+        const bool legacy = (flags & SBLAS_FLAG_SPLIT_MERGE) == 0;
+        const bool serial = (flags & SBLAS_FLAG_SPLIT_SERIAL) != 0;
+        auto kern = legacy ? (serial ? (vec ? spmv_split_kernel<T, kSpmvBlock, true, false> : spmv_split_kernel<T, kSpmvBlock, false, false>)
+                                     : (flags & SBLAS_FLAG_NO_L1)
+                                           ? (vec ? spmv_split_kernel<T, kSpmvBlock, true, true, true> : spmv_split_kernel<T, kSpmvBlock, false, true, true>)
+                                           : (vec ? spmv_split_kernel<T, kSpmvBlock, true, true> : spmv_split_kernel<T, kSpmvBlock, false, true>))
                            : (vec ? spmv_merge_kernel<T, kSpmvBlock, true> : spmv_merge_kernel<T, kSpmvBlock, false>);
+        if (flags & SBLAS_FLAG_SPLIT_SEG)
+          kern = vec ? spmv_split_seg_kernel<T, kSpmvBlock, true> : spmv_split_seg_kernel<T, kSpmvBlock, false>;
         if ((rc = set_smem_once<T>((const void*)kern, smem)) == 0) {
           kern<<<tt->n_tiles, kSpmvBlock, smem, st>>>(tt->d_tile_row, tile, rows, nnz, rp, ci, v, x,
                                                       sink, carry_out, head_val, head_row, cap);

@@ -59,7 +59,7 @@ MATS = {
 
 @pytest.mark.parametrize("dtype", [np.float64, np.float32])
 @pytest.mark.parametrize("mat", list(MATS))
-@pytest.mark.parametrize("variant", ["auto", "tile", "pipe", "pipe2", "vector", "split", "splitd", "split700", "splitl",
+@pytest.mark.parametrize("variant", ["auto", "tile", "pipe", "pipe2", "vector", "split", "splitd", "splits", "splitg", "splitg700", "splitgd", "splitm", "splitm700", "splitmd",
                                      "splitp", "noplan"])
 def test_spmv_vs_oracle(sblas, dev, oracle, dtype, mat, variant):
     import torch
@@ -74,15 +74,19 @@ def test_spmv_vs_oracle(sblas, dev, oracle, dtype, mat, variant):
     ref = oracle.spmv(rp, ci, v, x, y0.copy(), alpha, beta)
     drp, dci, dv, dx, dy = (_t(dev, a) for a in (rp, ci, v, x, y0))
     plan = None if variant == "noplan" else K.Plan(drp, len(ci))
-    # split = balanced merge-path phase 2 (default), splitd = its default tile, split700 = a tile that is not a
-    # multiple of the CTA size, splitl = the first (sub-warp per row) phase 2, splitp = staged flavour
+    # split = sub-warp per row phase 2 (default), splitd = its default tile, splitm* = balanced merge-path phase 2
+    # (tile 512, a tile that is not a multiple of the CTA size, the default tile), splits = row pointers before the
+    # A stream (first version), splitp = staged flavour
     var = dict(auto=0, noplan=0, tile=sblas.SPMV_TILE, vector=sblas.SPMV_VECTOR, split=sblas.SPMV_SPLIT,
-               splitd=sblas.SPMV_SPLIT, split700=sblas.SPMV_SPLIT, splitl=sblas.SPMV_SPLIT,
+               splitd=sblas.SPMV_SPLIT, splits=sblas.SPMV_SPLIT, splitg=sblas.SPMV_SPLIT, splitg700=sblas.SPMV_SPLIT,
+               splitgd=sblas.SPMV_SPLIT, splitm=sblas.SPMV_SPLIT, splitm700=sblas.SPMV_SPLIT, splitmd=sblas.SPMV_SPLIT,
                splitp=sblas.SPMV_SPLIT, pipe=sblas.SPMV_PIPE, pipe2=sblas.SPMV_PIPE)[variant]
-    opts = sblas.make_opts(variant=var, tile={"tile": 512, "split": 512, "split700": 700, "splitl": 512, "splitp": 512,
+    opts = sblas.make_opts(variant=var, tile={"tile": 512, "split": 512, "splits": 512, "splitg": 512, "splitg700": 700, "splitm": 512, "splitm700": 700, "splitp": 512,
                                               "pipe": 320, "pipe2": 3072}.get(variant, 0),
                            stages={"pipe": 4, "pipe2": 2, "splitp": 2}.get(variant, 0),
-                           flags=sblas.FLAG_SPLIT_LEGACY if variant == "splitl" else 0)
+                           flags=sblas.FLAG_SPLIT_MERGE if variant.startswith("splitm") else
+                           sblas.FLAG_SPLIT_SEG if variant.startswith("splitg") else
+                           sblas.FLAG_SPLIT_SERIAL if variant == "splits" else 0)
     K.spmv(drp, dci, dv, dx, dy, alpha, beta, plan=plan, opts=opts)
     torch.cuda.synchronize()
     bound = _row_bound(oracle, rp, ci, v, x, alpha, beta, y0)
