@@ -126,6 +126,9 @@ SBLAS_API int sblas_csr_partition_rows_i32(const int32_t* rowptr, int32_t height
 SBLAS_API int sblas_mtx_info(const char* filename, int32_t* m, int32_t* n, int32_t* nnz,
                              int32_t* is_symmetric);
 SBLAS_API int sblas_mtx_data(const char* filename, int32_t* rowptr, int32_t* colidx, double* val);
+/* host threads of the loader: 0 = automatic (hardware threads, >= 256 KB of text each; the
+ * environment variable SBLAS_MTX_THREADS overrides), 1 = serial.  The result does not depend on it. */
+SBLAS_API void sblas_mtx_set_threads(int n);
 
 /* ---- per-device CSR plan (tile tables + row statistics; built once at sync2gpu) ------ */
 typedef struct sblasPlan_st* sblasPlan_t;

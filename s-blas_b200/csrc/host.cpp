@@ -5,8 +5,12 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
+
+#include <sys/stat.h>
 
 #include "sblas_b200.h"
 
@@ -105,8 +109,24 @@ int sblas_csr_partition_rows_i32(const int32_t* rowptr, int32_t height, unsigned
 // Semantics of mmio_highlevel.h:7-127 / :130-281: pattern -> 1.0, integer read as int, complex
 // keeps the real part, symmetric or hermitian inputs mirrored (skew-symmetric is not), rows
 // filled by a counting sort in file order (mirrored entry right behind its original), columns
-// NOT sorted within a row.  The file is read in one gulp and tokenised by hand (the reference's
-// per-entry fscanf dominates its "Load Time" on SuiteSparse-size inputs).
+// NOT sorted within a row.
+//
+// SURVEY §8(f) f1 — the loader is the step right before the path (matrix.h:300-330) and the
+// reference's per-entry fscanf dominates its "Load Time" on SuiteSparse-size inputs.  Here the file
+// is read in one gulp and parsed by T host threads, order-preserving:
+//   1. the entry region is cut into T byte ranges that begin at token starts; every thread counts
+//      the whitespace-separated tokens that START in its range (the reference's fscanf is token-,
+//      not line-based, so entries may be wrapped over lines in any way);
+//   2. a prefix sum gives each range its first global token index g; entry e owns the tokens
+//      [e*tpe, (e+1)*tpe) (tpe = 2 pattern, 3 real/integer, 4 complex), so a thread skips to its
+//      first token with g % tpe == 0 and parses every entry that begins in its range (running
+//      past the range end for the last one) straight into slot e of the coordinate arrays;
+//   3. the CSR fill is a stable parallel counting sort: per-thread row histograms over contiguous
+//      entry ranges, turned into per-thread start offsets, so every row keeps FILE order and a
+//      mirrored entry sits right behind its original — bit-identical to the serial loop.
+// SBLAS_MTX_THREADS (or sblas_mtx_set_threads) bounds T; T = 1 is the plain serial loop.
+// sblas_mtx_info keeps the parsed file until the matching sblas_mtx_data call, so the usual
+// info -> allocate -> data sequence (matrix.h:303-318) parses the file once, not twice.
 namespace {
 struct Mtx {
   int m = 0, n = 0, sym = 0;
@@ -114,13 +134,63 @@ struct Mtx {
   std::vector<double> v;
 };
 
+int g_mtx_threads = 0;  // 0 = auto
+
+static inline bool is_ws(char c) { return c == ' ' || c == '\n' || c == '\t' || c == '\r' || c == '\v' || c == '\f'; }
 static const char* skip_ws(const char* p, const char* e) {
-  while (p < e && isspace((unsigned char)*p)) ++p;
+  while (p < e && is_ws(*p)) ++p;
+  return p;
+}
+static const char* skip_tok(const char* p, const char* e) {
+  while (p < e && !is_ws(*p)) ++p;
   return p;
 }
 static const char* next_line(const char* p, const char* e) {
   while (p < e && *p != '\n') ++p;
   return p < e ? p + 1 : e;
+}
+
+static int mtx_thread_count(size_t bytes) {
+  int t = g_mtx_threads;
+  if (t <= 0) {
+    if (const char* s = getenv("SBLAS_MTX_THREADS")) t = atoi(s);
+  }
+  if (t <= 0) {
+    t = (int)std::thread::hardware_concurrency();
+    if (t <= 0) t = 1;
+    t = std::min(t, 64);
+    t = (int)std::min<size_t>((size_t)t, std::max<size_t>(1, bytes >> 18));  // >= 256 KB of text per thread
+  }
+  return std::max(1, std::min(t, 256));
+}
+
+template <typename F>
+static void run_threads(int T, F&& fn) {
+  if (T <= 1) { fn(0); return; }
+  std::vector<std::thread> th;
+  th.reserve((size_t)T - 1);
+  for (int t = 1; t < T; ++t) th.emplace_back([&fn, t] { fn(t); });
+  fn(0);
+  for (auto& x : th) x.join();
+}
+
+enum Field { F_REAL, F_CPLX, F_INT, F_PAT };
+
+// parse one entry whose first token starts at p; returns the position behind its last token
+static inline const char* parse_entry(const char* p, const char* e, Field fld, int32_t* r, int32_t* c, double* x) {
+  char* q = nullptr;
+  long a = strtol(p, &q, 10); p = skip_tok(q > p ? q : p, e); p = skip_ws(p, e);
+  long b = strtol(p, &q, 10); p = skip_tok(q > p ? q : p, e);
+  double val = 1.0;
+  if (fld == F_REAL) { p = skip_ws(p, e); val = strtod(p, &q); p = skip_tok(q > p ? q : p, e); }
+  else if (fld == F_CPLX) {
+    p = skip_ws(p, e); val = strtod(p, &q); p = skip_tok(q > p ? q : p, e);
+    p = skip_ws(p, e); p = skip_tok(p, e);  // imaginary part dropped (mmio_highlevel.h:192)
+  } else if (fld == F_INT) { p = skip_ws(p, e); val = (double)(int)strtol(p, &q, 10); p = skip_tok(q > p ? q : p, e); }
+  *r = (int32_t)(a - 1);
+  *c = (int32_t)(b - 1);
+  *x = val;
+  return p;
 }
 
 static int load_mtx(const char* fn, Mtx& M) {
@@ -129,10 +199,10 @@ static int load_mtx(const char* fn, Mtx& M) {
   fseek(f, 0, SEEK_END);
   long sz = ftell(f);
   fseek(f, 0, SEEK_SET);
-  std::string buf((size_t)std::max(sz, 0l), '\0');
+  std::string buf((size_t)std::max(sz, 0l) + 1, '\0');  // NUL behind the text: strtol/strtod stop there
   if (sz > 0 && fread(&buf[0], 1, (size_t)sz, f) != (size_t)sz) { fclose(f); set_error("mtx: short read"); return -1; }
   fclose(f);
-  const char *p = buf.data(), *e = p + buf.size();
+  const char *p = buf.data(), *e = p + (size_t)std::max(sz, 0l);
   // banner: %%MatrixMarket matrix coordinate <type> <symmetry>
   char w[5][64] = {{0}};
   {
@@ -150,6 +220,8 @@ static int load_mtx(const char* fn, Mtx& M) {
   const bool is_real = !strcmp(w[3], "real"), is_cplx = !strcmp(w[3], "complex"),
              is_int = !strcmp(w[3], "integer"), is_pat = !strcmp(w[3], "pattern");
   if (!(is_real || is_cplx || is_int || is_pat)) { set_error("mtx: unknown field type '%s'", w[3]); return -2; }
+  const Field fld = is_real ? F_REAL : is_cplx ? F_CPLX : is_int ? F_INT : F_PAT;
+  const int tpe = is_pat ? 2 : is_cplx ? 4 : 3;  // tokens per entry
   M.sym = (!strcmp(w[4], "symmetric") || !strcmp(w[4], "hermitian")) ? 1 : 0;
   while (p < e && *p == '%') p = next_line(p, e);  // comments
   long nz = 0;
@@ -161,30 +233,76 @@ static int load_mtx(const char* fn, Mtx& M) {
     if (M.m < 0 || M.n < 0 || nz < 0) { set_error("mtx: bad size line"); return -4; }
   }
   M.ri.resize((size_t)nz); M.cj.resize((size_t)nz); M.v.resize((size_t)nz);
-  for (long i = 0; i < nz; ++i) {
-    char* q = nullptr;
-    p = skip_ws(p, e);
-    if (p >= e) { set_error("mtx: %ld entries announced, %ld found", nz, i); return -5; }
-    long a = strtol(p, &q, 10); p = q;
-    long b = strtol(p, &q, 10); p = q;
-    double x = 1.0;
-    if (is_real) { x = strtod(p, &q); p = q; }
-    else if (is_cplx) { x = strtod(p, &q); p = q; (void)strtod(p, &q); p = q; }
-    else if (is_int) { x = (double)(int)strtol(p, &q, 10); p = q; }
-    M.ri[(size_t)i] = (int32_t)(a - 1);
-    M.cj[(size_t)i] = (int32_t)(b - 1);
-    M.v[(size_t)i] = x;
+  p = skip_ws(p, e);
+  const size_t len = (size_t)(e - p);
+  const int T = mtx_thread_count(len);
+  // 1. range starts at token starts
+  std::vector<const char*> start((size_t)T + 1);
+  start[0] = p;
+  start[(size_t)T] = e;
+  for (int t = 1; t < T; ++t) {
+    const char* q = p + len * (size_t)t / (size_t)T;
+    if (q > p && !is_ws(q[-1])) q = skip_tok(q, e);  // inside a token: it belongs to the range before
+    start[(size_t)t] = skip_ws(q, e);
   }
+  for (int t = 1; t <= T; ++t) start[(size_t)t] = std::max(start[(size_t)t], start[(size_t)t - 1]);
+  std::vector<long> ntok((size_t)T + 1, 0);
+  run_threads(T, [&](int t) {
+    const char *q = start[(size_t)t], *qe = start[(size_t)t + 1];
+    long c = 0;
+    while (q < qe) { ++c; q = skip_tok(q, e); q = skip_ws(q, e); }  // a token that starts here counts here
+    ntok[(size_t)t + 1] = c;
+  });
+  // 2. first global token index of every range
+  for (int t = 0; t < T; ++t) ntok[(size_t)t + 1] += ntok[(size_t)t];
+  if (ntok[(size_t)T] < nz * tpe) {
+    set_error("mtx: %ld entries announced, %ld found", nz, ntok[(size_t)T] / tpe);
+    return -5;
+  }
+  run_threads(T, [&](int t) {
+    const char *q = start[(size_t)t], *qe = start[(size_t)t + 1];
+    long g = ntok[(size_t)t];
+    while (q < qe && g % tpe != 0) { q = skip_tok(q, e); q = skip_ws(q, e); ++g; }  // tail of the previous range's entry
+    long i = g / tpe;
+    while (q < qe && i < nz) {
+      q = parse_entry(q, e, fld, &M.ri[(size_t)i], &M.cj[(size_t)i], &M.v[(size_t)i]);
+      q = skip_ws(q, e);
+      ++i;
+    }
+  });
   return 0;
+}
+
+// the file parsed by the last sblas_mtx_info, kept for the sblas_mtx_data call that follows it
+struct MtxCache {
+  std::mutex mu;
+  std::string key;
+  Mtx M;
+  bool valid = false;
+} g_mtx_cache;
+
+static std::string mtx_key(const char* fn) {
+  struct stat st;
+  if (stat(fn, &st) != 0) return std::string();
+  char b[96];
+  snprintf(b, sizeof b, "|%lld|%lld|%lld", (long long)st.st_size, (long long)st.st_mtime, (long long)st.st_ino);
+  return std::string(fn) + b;
 }
 }  // namespace
 
 extern "C" {
 
+void sblas_mtx_set_threads(int n) { g_mtx_threads = n; }
+
 int sblas_mtx_info(const char* fn, int32_t* m, int32_t* n, int32_t* nnz, int32_t* is_sym) {
-  Mtx M;
+  std::lock_guard<std::mutex> lk(g_mtx_cache.mu);
+  Mtx& M = g_mtx_cache.M;
+  g_mtx_cache.valid = false;
+  M = Mtx();
   int rc = load_mtx(fn, M);
   if (rc) return rc;
+  g_mtx_cache.key = mtx_key(fn);
+  g_mtx_cache.valid = !g_mtx_cache.key.empty();
   int64_t tot = (int64_t)M.ri.size();
   if (M.sym) for (size_t i = 0; i < M.ri.size(); ++i) tot += (M.ri[i] != M.cj[i]);
   if (m) *m = M.m;
@@ -195,31 +313,68 @@ int sblas_mtx_info(const char* fn, int32_t* m, int32_t* n, int32_t* nnz, int32_t
 }
 
 int sblas_mtx_data(const char* fn, int32_t* rowptr, int32_t* colidx, double* val) {
-  Mtx M;
-  int rc = load_mtx(fn, M);
-  if (rc) return rc;
+  std::lock_guard<std::mutex> lk(g_mtx_cache.mu);
+  Mtx local;
+  Mtx* pM = &local;
+  if (g_mtx_cache.valid && g_mtx_cache.key == mtx_key(fn)) {
+    pM = &g_mtx_cache.M;
+  } else {
+    int rc = load_mtx(fn, local);
+    if (rc) return rc;
+  }
+  Mtx& M = *pM;
+  struct Drop { ~Drop() { g_mtx_cache.valid = false; g_mtx_cache.M = Mtx(); } } drop;  // one data call per info call
   const size_t nz = M.ri.size();
-  std::vector<int32_t> cnt((size_t)M.m + 1, 0);
-  for (size_t i = 0; i < nz; ++i) {
-    if (M.ri[i] < 0 || M.ri[i] >= M.m || M.cj[i] < 0 || M.cj[i] >= M.n) { set_error("mtx: entry %zu out of range", i); return -6; }
-    cnt[(size_t)M.ri[i]]++;
-    if (M.sym && M.ri[i] != M.cj[i]) {
-      if (M.cj[i] >= M.m) { set_error("mtx: symmetric matrix is not square"); return -6; }
-      cnt[(size_t)M.cj[i]]++;
+  const size_t m1 = (size_t)M.m + 1;
+  // threads for the counting sort: contiguous entry ranges, one row histogram each (<= 256 MB in all)
+  int T = mtx_thread_count(nz * 24);
+  T = (int)std::min<size_t>((size_t)T, std::max<size_t>(1, ((size_t)256 << 20) / (m1 * sizeof(int32_t))));
+  std::vector<int32_t> hist((size_t)T * m1, 0);
+  std::vector<int> bad((size_t)T, 0);
+  std::vector<size_t> bad_at((size_t)T, 0);
+  auto lo_of = [&](int t) { return nz * (size_t)t / (size_t)T; };
+  run_threads(T, [&](int t) {
+    int32_t* h = &hist[(size_t)t * m1];
+    for (size_t i = lo_of(t); i < lo_of(t + 1); ++i) {
+      const int32_t r = M.ri[i], c = M.cj[i];
+      if (r < 0 || r >= M.m || c < 0 || c >= M.n) { if (!bad[(size_t)t]) { bad[(size_t)t] = 1; bad_at[(size_t)t] = i; } continue; }
+      h[r]++;
+      if (M.sym && r != c) {
+        if (c >= M.m) { if (!bad[(size_t)t]) { bad[(size_t)t] = 2; bad_at[(size_t)t] = i; } continue; }
+        h[c]++;
+      }
     }
+  });
+  for (int t = 0; t < T; ++t) {
+    if (bad[(size_t)t] == 1) { set_error("mtx: entry %zu out of range", bad_at[(size_t)t]); return -6; }
+    if (bad[(size_t)t] == 2) { set_error("mtx: symmetric matrix is not square"); return -6; }
   }
-  int32_t acc = 0;
-  for (int i = 0; i <= M.m; ++i) { int32_t c = cnt[(size_t)i]; rowptr[i] = acc; acc += c; }
-  std::fill(cnt.begin(), cnt.end(), 0);
-  for (size_t i = 0; i < nz; ++i) {
-    const int32_t r = M.ri[i], c = M.cj[i];
-    int32_t o = rowptr[r] + cnt[(size_t)r]++;
-    colidx[o] = c; val[o] = M.v[i];
-    if (M.sym && r != c) {
-      o = rowptr[c] + cnt[(size_t)c]++;
-      colidx[o] = r; val[o] = M.v[i];
+  // row totals -> rowptr; hist[t][r] becomes thread t's first slot in row r
+  int64_t acc = 0;
+  for (size_t r = 0; r < (size_t)M.m; ++r) {
+    rowptr[r] = (int32_t)acc;
+    int64_t run = acc;
+    for (int t = 0; t < T; ++t) {
+      int32_t& h = hist[(size_t)t * m1 + r];
+      const int32_t c = h;
+      h = (int32_t)run;
+      run += c;
     }
+    acc = run;
   }
+  rowptr[M.m] = (int32_t)acc;
+  run_threads(T, [&](int t) {
+    int32_t* h = &hist[(size_t)t * m1];
+    for (size_t i = lo_of(t); i < lo_of(t + 1); ++i) {
+      const int32_t r = M.ri[i], c = M.cj[i];
+      int32_t o = h[r]++;
+      colidx[o] = c; val[o] = M.v[i];
+      if (M.sym && r != c) {
+        o = h[c]++;
+        colidx[o] = r; val[o] = M.v[i];
+      }
+    }
+  });
   return 0;
 }
 

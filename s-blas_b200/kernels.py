@@ -74,8 +74,10 @@ def csr_partition_rows(rowptr, n_gpu):
     return out
 
 
-def read_mtx(path):
-    """mmio_highlevel.h:7,130 -> (h, w, rowptr, colidx, val[f64]) in file order."""
+def read_mtx(path, threads=None):
+    """mmio_highlevel.h:7,130 -> (h, w, rowptr, colidx, val[f64]) in file order.  `threads`: host
+    threads of the parser / counting sort (None or 0 = automatic, 1 = serial); same result for any."""
+    lib().sblas_mtx_set_threads(C.c_int(int(threads or 0)))
     m, n, nnz, sym = C.c_int32(), C.c_int32(), C.c_int32(), C.c_int32()
     check(lib().sblas_mtx_info(path.encode(), C.byref(m), C.byref(n), C.byref(nnz), C.byref(sym)),
           "mtx_info")

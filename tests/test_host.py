@@ -93,6 +93,50 @@ def test_mtx_loader_against_reference(sblas, reference, tmp_path):
             assert np.array_equal(x, y)
 
 
+@pytest.mark.parametrize("kind", ["real general", "real symmetric", "pattern symmetric", "integer general",
+                                  "complex hermitian"])
+def test_mtx_loader_parallel_is_order_preserving(sblas, oracle, tmp_path, kind):
+    """the multi-threaded parser + stable counting sort returns exactly what the serial
+    loop (and the oracle's restatement of mmio_highlevel.h:130-281) returns, for any thread count, with
+    unsorted entries, duplicates, comment lines and entries wrapped over lines in odd ways."""
+    rng = np.random.default_rng(len(kind))
+    field, symm = kind.split()
+    n, nz = 300, 20000
+    r, c = rng.integers(1, n + 1, nz), rng.integers(1, n + 1, nz)
+    if symm != "general":
+        r, c = np.maximum(r, c), np.minimum(r, c)
+    seps = [" ", "  ", "\t", "\n", " \n ", "\r\n"]
+    p = tmp_path / "m.mtx"
+    with open(p, "w", newline="") as f:
+        f.write("%%%%MatrixMarket matrix coordinate %s %s\n%% comment\n%%another\n %d %d %d\n" % (field, symm, n, n, nz))
+        for i in range(nz):
+            toks = [str(r[i]), str(c[i])]
+            if field == "real":
+                toks.append("%.17g" % rng.standard_normal())
+            elif field == "integer":
+                toks.append(str(int(rng.integers(-50, 50))))
+            elif field == "complex":
+                toks += ["%.6e" % rng.standard_normal(), "%g" % rng.standard_normal()]
+            # mostly one entry per line, sometimes wrapped or run together like fscanf tolerates
+            odd = rng.random() < 0.2
+            f.write((seps[int(rng.integers(len(seps)))] if odd else " ").join(toks))
+            f.write(seps[int(rng.integers(len(seps)))] if odd else "\n")
+    ref = oracle.read_mtx(str(p))
+    for t in (1, 2, 3, 5, 16):
+        got = sblas.kernels.read_mtx(str(p), threads=t)
+        assert got[0] == ref[0] and got[1] == ref[1]
+        for x, y in zip(got[2:], ref[2:]):
+            assert np.array_equal(x, y), (kind, t)
+    sblas.kernels.read_mtx(str(p), threads=0)
+
+
+def test_mtx_loader_short_file_is_an_error(sblas, tmp_path):
+    p = tmp_path / "short.mtx"
+    p.write_text("%%MatrixMarket matrix coordinate real general\n3 3 4\n1 1 1.0\n2 2 2.0\n3 3\n")
+    with pytest.raises(sblas.SblasError):
+        sblas.kernels.read_mtx(str(p), threads=2)
+
+
 @pytest.mark.parametrize("n", [1, 2, 3, 4, 8])
 def test_partition_matches_golden(sblas, golden, n):
     p = sblas.kernels.csr_partition_nnz(golden["ash_rp"], n)
