@@ -17,8 +17,10 @@
  *     only uses this class sees the reference's col-major semantics.  Set the environment
  *     variable SBLAS_DENSE_DEVICE_LAYOUT=col (or dev_layout before sync2gpu) to keep the
  *     reference's device layout; the ops accept both.
- * COO / CSC containers and CsrToCsc / CscToCsr (matrix.h:40-272, :457-506) are not on the
- * SpMV/SpMM path and are not part of this build.
+ * COO / CSC containers and CsrToCsc / CscToCsr (matrix.h:40-272, :457-506) keep
+ * their names, signatures and field names; the conversions and the COO sort run on GPU 0
+ * (sblas_compressed_transpose_on / sblas_coo_sort_on: stable radix sort + gather), bit-identical to
+ * the reference's CPU loops.
  * IdxType must be a 32-bit integer type (the only kind the reference's ops are instantiated
  * with, unit_test.cu:81); DataType is float or double. */
 #ifndef MATRIX_H
@@ -29,11 +31,190 @@
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
+#include <iostream>
 
 #include "utility.h"
 
 enum GpuSharePolicy { none = 0, replicate = 1, segment = 2 }; /* matrix.h:34 */
 enum MajorOrder { row_major = 0, col_major = 1 };             /* matrix.h:37 */
+
+/* ============================ CSR <-> CSC conversion ============================ */
+namespace sblas_convert_detail {
+/* host arrays in, host arrays out, the work on logical GPU 0 */
+template <typename IdxType, typename DataType>
+inline void transpose_on_gpu0(IdxType m, IdxType n, IdxType nnz, const IdxType* ptr, const IdxType* idx,
+                              const DataType* val, IdxType* out_idx, IdxType* out_ptr, DataType* out_val) {
+  static_assert(sizeof(IdxType) == 4, "the B200 build supports 32-bit indices (sblas_b200.h)");
+  static_assert(sizeof(DataType) == 4 || sizeof(DataType) == 8, "DataType must be float or double");
+  const size_t nz = (size_t)nnz, pb = ((size_t)m + 1) * 4, ob = ((size_t)n + 1) * 4;
+  int32_t *d_ptr = NULL, *d_idx = NULL, *d_optr = NULL, *d_oidx = NULL;
+  void *d_val = NULL, *d_oval = NULL;
+  SAFE_ALOC_GPU_ON(0, d_ptr, pb);
+  SAFE_ALOC_GPU_ON(0, d_optr, ob);
+  SAFE_ALOC_GPU_ON(0, d_idx, std::max<size_t>(nz * 4, 16));
+  SAFE_ALOC_GPU_ON(0, d_oidx, std::max<size_t>(nz * 4, 16));
+  SAFE_ALOC_GPU_ON(0, d_val, std::max<size_t>(nz * sizeof(DataType), 16));
+  SAFE_ALOC_GPU_ON(0, d_oval, std::max<size_t>(nz * sizeof(DataType), 16));
+  SBLAS_SAFE_CALL(sblas_copy_h2d(0, d_ptr, ptr, pb));
+  if (nz) {
+    SBLAS_SAFE_CALL(sblas_copy_h2d(0, d_idx, idx, nz * 4));
+    SBLAS_SAFE_CALL(sblas_copy_h2d(0, d_val, val, nz * sizeof(DataType)));
+  }
+  SBLAS_SAFE_CALL(sblas_compressed_transpose_on(0, sizeof(DataType) == 8, (int32_t)m, (int32_t)n, (int64_t)nnz, d_ptr,
+                                                d_idx, d_val, d_optr, d_oidx, d_oval));
+  SBLAS_SAFE_CALL(sblas_copy_d2h(0, out_ptr, d_optr, ob));
+  if (nz) {
+    SBLAS_SAFE_CALL(sblas_copy_d2h(0, out_idx, d_oidx, nz * 4));
+    SBLAS_SAFE_CALL(sblas_copy_d2h(0, out_val, d_oval, nz * sizeof(DataType)));
+  }
+  SAFE_FREE_GPU_ON(0, d_ptr);
+  SAFE_FREE_GPU_ON(0, d_optr);
+  SAFE_FREE_GPU_ON(0, d_idx);
+  SAFE_FREE_GPU_ON(0, d_oidx);
+  SAFE_FREE_GPU_ON(0, d_val);
+  SAFE_FREE_GPU_ON(0, d_oval);
+}
+}  // namespace sblas_convert_detail
+
+/* matrix.h:40-64 — same signature (host arrays); inside a column the entries keep CSR order */
+template <typename IdxType, typename DataType>
+void CsrToCsc(const IdxType m, const IdxType n, const IdxType nnz, const IdxType* csrRowPtr, const IdxType* csrColIdx,
+              const DataType* csrVal, IdxType* cscRowIdx, IdxType* cscColPtr, DataType* cscVal) {
+  sblas_convert_detail::transpose_on_gpu0<IdxType, DataType>(m, n, nnz, csrRowPtr, csrColIdx, csrVal, cscRowIdx,
+                                                            cscColPtr, cscVal);
+}
+/* matrix.h:67-91 — note the reference's argument order: (n, m, ...) */
+template <typename IdxType, typename DataType>
+void CscToCsr(const IdxType n, const IdxType m, const IdxType nnz, const IdxType* cscColPtr, const IdxType* cscRowIdx,
+              const DataType* cscVal, IdxType* csrColIdx, IdxType* csrRowPtr, DataType* csrVal) {
+  sblas_convert_detail::transpose_on_gpu0<IdxType, DataType>(n, m, nnz, cscColPtr, cscRowIdx, cscVal, csrColIdx,
+                                                            csrRowPtr, csrVal);
+}
+
+/* ================================== COO matrix ================================== */
+/* matrix.h:117-272.  Loaded from a Matrix Market file as the file holds it (no symmetric expansion,
+ * matrix.h:165-173), sorted by (row, col) on the device, then replicated or cut into
+ * floor(nnz / n_gpu)-sized pieces exactly like matrix.h:196-216 (trailing nnz % n_gpu entries stay
+ * on the host only, as in the reference). */
+template <typename IdxType, typename DataType>
+class CooSparseMatrix {
+  static_assert(sizeof(IdxType) == 4, "the B200 build supports 32-bit indices (sblas_b200.h)");
+
+ public:
+  CooSparseMatrix() { clear_(); }
+  explicit CooSparseMatrix(const char* filename, unsigned _n_gpu = 0, enum GpuSharePolicy _policy = none) {
+    clear_();
+    std::cout << "Loading input matrix from '" << filename << "'." << std::endl;
+    int32_t m = 0, n = 0, nz = 0;
+    SBLAS_SAFE_CALL(sblas_mtx_coo_info(filename, &m, &n, &nz));
+    height = (IdxType)m;
+    width = (IdxType)n;
+    nnz = (IdxType)nz;
+    std::cout << "Height: " << height << " Width: " << width << " nnz: " << nnz << std::endl;
+    SAFE_ALOC_HOST(cooRowIdx, std::max<size_t>(get_nnz_idx_size(), 16));
+    SAFE_ALOC_HOST(cooColIdx, std::max<size_t>(get_nnz_idx_size(), 16));
+    SAFE_ALOC_HOST(cooVal, std::max<size_t>(get_nnz_val_size(), 16));
+    double* tmp = (double*)malloc(sizeof(double) * (size_t)std::max(nz, 1));
+    SBLAS_SAFE_CALL(sblas_mtx_coo_data(filename, (int32_t*)cooRowIdx, (int32_t*)cooColIdx, tmp));
+    for (int32_t j = 0; j < nz; j++) cooVal[j] = (DataType)tmp[j];
+    free(tmp);
+    sortByRow();
+    n_gpu = _n_gpu;
+    policy = _policy;
+    if (n_gpu != 0 && policy != none) {
+      SAFE_ALOC_HOST(cooRowIdx_gpu, n_gpu * sizeof(IdxType*));
+      SAFE_ALOC_HOST(cooColIdx_gpu, n_gpu * sizeof(IdxType*));
+      SAFE_ALOC_HOST(cooVal_gpu, n_gpu * sizeof(DataType*));
+      SAFE_ALOC_HOST(nnz_gpu, n_gpu * sizeof(IdxType));
+      const IdxType avg_nnz = nnz / (IdxType)n_gpu; /* matrix.h:198: ceil() of an integer quotient */
+      for (unsigned i = 0; i < n_gpu; i++) {
+        const IdxType first = policy == segment ? (IdxType)i * avg_nnz : 0;
+        nnz_gpu[i] = policy == segment ? std::min((IdxType)(i + 1) * avg_nnz, nnz) - first : nnz;
+        cooRowIdx_gpu[i] = cooColIdx_gpu[i] = NULL;
+        cooVal_gpu[i] = NULL;
+        SAFE_ALOC_GPU_ON(i, cooRowIdx_gpu[i], std::max<size_t>(get_gpu_nnz_idx_size(i), 16));
+        SAFE_ALOC_GPU_ON(i, cooColIdx_gpu[i], std::max<size_t>(get_gpu_nnz_idx_size(i), 16));
+        SAFE_ALOC_GPU_ON(i, cooVal_gpu[i], std::max<size_t>(get_gpu_nnz_val_size(i), 16));
+        if (nnz_gpu[i] > 0) {
+          SBLAS_SAFE_CALL(sblas_copy_h2d((int)i, cooRowIdx_gpu[i], cooRowIdx + first, get_gpu_nnz_idx_size(i)));
+          SBLAS_SAFE_CALL(sblas_copy_h2d((int)i, cooColIdx_gpu[i], cooColIdx + first, get_gpu_nnz_idx_size(i)));
+          SBLAS_SAFE_CALL(sblas_copy_h2d((int)i, cooVal_gpu[i], cooVal + first, get_gpu_nnz_val_size(i)));
+        }
+      }
+    }
+  }
+  ~CooSparseMatrix() {
+    SAFE_FREE_HOST(cooRowIdx);
+    SAFE_FREE_HOST(cooColIdx);
+    SAFE_FREE_HOST(cooVal);
+    if (cooRowIdx_gpu != NULL) {
+      for (unsigned i = 0; i < n_gpu; i++) {
+        SAFE_FREE_GPU_ON(i, cooRowIdx_gpu[i]);
+        SAFE_FREE_GPU_ON(i, cooColIdx_gpu[i]);
+        SAFE_FREE_GPU_ON(i, cooVal_gpu[i]);
+      }
+      SAFE_FREE_HOST(cooRowIdx_gpu);
+      SAFE_FREE_HOST(cooColIdx_gpu);
+      SAFE_FREE_HOST(cooVal_gpu);
+    }
+    SAFE_FREE_HOST(nnz_gpu);
+  }
+  /* matrix.h:221-237 — by (row, col); equal pairs keep file order */
+  void sortByRow() {
+    if (nnz <= 0) return;
+    int32_t *d_r = NULL, *d_c = NULL;
+    void* d_v = NULL;
+    SAFE_ALOC_GPU_ON(0, d_r, get_nnz_idx_size());
+    SAFE_ALOC_GPU_ON(0, d_c, get_nnz_idx_size());
+    SAFE_ALOC_GPU_ON(0, d_v, get_nnz_val_size());
+    SBLAS_SAFE_CALL(sblas_copy_h2d(0, d_r, cooRowIdx, get_nnz_idx_size()));
+    SBLAS_SAFE_CALL(sblas_copy_h2d(0, d_c, cooColIdx, get_nnz_idx_size()));
+    SBLAS_SAFE_CALL(sblas_copy_h2d(0, d_v, cooVal, get_nnz_val_size()));
+    SBLAS_SAFE_CALL(sblas_coo_sort_on(0, sizeof(DataType) == 8, (int64_t)nnz, (int32_t)height, d_r, d_c, d_v));
+    SBLAS_SAFE_CALL(sblas_copy_d2h(0, cooRowIdx, d_r, get_nnz_idx_size()));
+    SBLAS_SAFE_CALL(sblas_copy_d2h(0, cooColIdx, d_c, get_nnz_idx_size()));
+    SBLAS_SAFE_CALL(sblas_copy_d2h(0, cooVal, d_v, get_nnz_val_size()));
+    SAFE_FREE_GPU_ON(0, d_r);
+    SAFE_FREE_GPU_ON(0, d_c);
+    SAFE_FREE_GPU_ON(0, d_v);
+  }
+  size_t get_gpu_nnz_idx_size(unsigned i_gpu) {
+    assert(i_gpu < n_gpu);
+    return nnz_gpu != NULL ? (size_t)nnz_gpu[i_gpu] * sizeof(IdxType) : 0;
+  }
+  size_t get_gpu_nnz_val_size(unsigned i_gpu) {
+    assert(i_gpu < n_gpu);
+    return nnz_gpu != NULL ? (size_t)nnz_gpu[i_gpu] * sizeof(DataType) : 0;
+  }
+  size_t get_nnz_idx_size() { return (size_t)nnz * sizeof(IdxType); }
+  size_t get_nnz_val_size() { return (size_t)nnz * sizeof(DataType); }
+
+ public: /* matrix.h:255-271 */
+  IdxType* cooRowIdx;
+  IdxType* cooColIdx;
+  DataType* cooVal;
+  IdxType** cooRowIdx_gpu;
+  IdxType** cooColIdx_gpu;
+  DataType** cooVal_gpu;
+  IdxType* nnz_gpu;
+  IdxType nnz;
+  IdxType height;
+  IdxType width;
+  unsigned n_gpu;
+  enum GpuSharePolicy policy;
+
+ private:
+  void clear_() {
+    cooRowIdx = cooColIdx = NULL;
+    cooVal = NULL;
+    cooRowIdx_gpu = cooColIdx_gpu = NULL;
+    cooVal_gpu = NULL;
+    nnz_gpu = NULL;
+    nnz = height = width = 0;
+    n_gpu = 0;
+    policy = none;
+  }
+};
 
 /* ================================== CSR matrix ================================== */
 template <typename IdxType, typename DataType>
@@ -204,6 +385,43 @@ class CsrSparseMatrix {
     SAFE_FREE_HOST(starting_row_gpu);
     SAFE_FREE_HOST(stoping_row_gpu);
   }
+};
+
+/* ================================== CSC matrix ================================== */
+/* matrix.h:457-506 — built from a CSR matrix by CsrToCsc (on the device, see above) */
+template <typename IdxType, typename DataType>
+class CscSparseMatrix {
+ public:
+  CscSparseMatrix() : cscRowIdx(NULL), cscColPtr(NULL), cscVal(NULL), nnz(0), height(0), width(0) {}
+  explicit CscSparseMatrix(const CsrSparseMatrix<IdxType, DataType>* csr)
+      : cscRowIdx(NULL), cscColPtr(NULL), cscVal(NULL) {
+    height = csr->height;
+    width = csr->width;
+    nnz = csr->nnz;
+    std::cout << "Building csc matrix from a csr matrix." << std::endl;
+    std::cout << "Height: " << height << " Width: " << width << " nnz: " << nnz << std::endl;
+    SAFE_ALOC_HOST(cscColPtr, get_col_ptr_size());
+    SAFE_ALOC_HOST(cscRowIdx, std::max<size_t>(get_row_idx_size(), 16));
+    SAFE_ALOC_HOST(cscVal, std::max<size_t>(get_val_size(), 16));
+    CsrToCsc<IdxType, DataType>(height, width, nnz, csr->csrRowPtr, csr->csrColIdx, csr->csrVal, cscRowIdx, cscColPtr,
+                                cscVal);
+  }
+  ~CscSparseMatrix() {
+    SAFE_FREE_HOST(cscColPtr);
+    SAFE_FREE_HOST(cscRowIdx);
+    SAFE_FREE_HOST(cscVal);
+  }
+  size_t get_col_ptr_size() { return ((size_t)width + 1) * sizeof(IdxType); }
+  size_t get_row_idx_size() { return (size_t)nnz * sizeof(IdxType); }
+  size_t get_val_size() { return (size_t)nnz * sizeof(DataType); }
+
+ public: /* matrix.h:499-505 */
+  IdxType* cscRowIdx;
+  IdxType* cscColPtr;
+  DataType* cscVal;
+  IdxType nnz;
+  IdxType height;
+  IdxType width;
 };
 
 /* device layout a col_major DenseMatrix gets on sync2gpu unless overridden per object */

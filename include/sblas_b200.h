@@ -129,6 +129,35 @@ SBLAS_API int sblas_mtx_data(const char* filename, int32_t* rowptr, int32_t* col
 /* host threads of the loader: 0 = automatic (hardware threads, >= 256 KB of text each; the
  * environment variable SBLAS_MTX_THREADS overrides), 1 = serial.  The result does not depend on it. */
 SBLAS_API void sblas_mtx_set_threads(int n);
+/* The coordinate entries as the file holds them (no symmetric expansion), 0-based, file order: what
+ * CooSparseMatrix(const char*) reads (matrix.h:142-176).  pattern files give 1.0 (the reference's
+ * "%d %d %lg" would misread them); nz = the announced entry count. */
+SBLAS_API int sblas_mtx_coo_info(const char* filename, int32_t* m, int32_t* n, int32_t* nz);
+SBLAS_API int sblas_mtx_coo_data(const char* filename, int32_t* rowidx, int32_t* colidx, double* val);
+
+/* ---- format containers beside CSR (matrix.h:40-272, :457-506), on the device ----
+ * CsrToCsc (matrix.h:40-64): stable by column — inside a column the entries keep CSR order —
+ * bit-identical to the reference's CPU loop.  CscToCsr (matrix.h:67-91) is the mirror image; note
+ * the reference's argument order (n, m, ...).  All pointers are device pointers on the stream's
+ * device; the call returns after the conversion finished (temporaries are released). */
+SBLAS_API int sblas_csr2csc_f64(void* stream, int32_t m, int32_t n, int64_t nnz, const int32_t* d_rowptr,
+                                const int32_t* d_colidx, const double* d_val, int32_t* d_cscColPtr,
+                                int32_t* d_cscRowIdx, double* d_cscVal);
+SBLAS_API int sblas_csr2csc_f32(void* stream, int32_t m, int32_t n, int64_t nnz, const int32_t* d_rowptr,
+                                const int32_t* d_colidx, const float* d_val, int32_t* d_cscColPtr,
+                                int32_t* d_cscRowIdx, float* d_cscVal);
+SBLAS_API int sblas_csc2csr_f64(void* stream, int32_t n, int32_t m, int64_t nnz, const int32_t* d_colptr,
+                                const int32_t* d_rowidx, const double* d_val, int32_t* d_csrRowPtr,
+                                int32_t* d_csrColIdx, double* d_csrVal);
+SBLAS_API int sblas_csc2csr_f32(void* stream, int32_t n, int32_t m, int64_t nnz, const int32_t* d_colptr,
+                                const int32_t* d_rowidx, const float* d_val, int32_t* d_csrRowPtr,
+                                int32_t* d_csrColIdx, float* d_csrVal);
+/* CooSparseMatrix::sortByRow (matrix.h:221-237): in-place sort by (row, col); equal pairs keep their
+ * order (the reference's qsort leaves that open). */
+SBLAS_API int sblas_coo_sort_f64(void* stream, int64_t nnz, int32_t height, int32_t* d_row, int32_t* d_col,
+                                 double* d_val);
+SBLAS_API int sblas_coo_sort_f32(void* stream, int64_t nnz, int32_t height, int32_t* d_row, int32_t* d_col,
+                                 float* d_val);
 
 /* ---- per-device CSR plan (tile tables + row statistics; built once at sync2gpu) ------ */
 typedef struct sblasPlan_st* sblasPlan_t;
@@ -235,6 +264,14 @@ SBLAS_API int sblas_axpby_on(int gpu, int is_f64, void* d_v0, const void* d_v1, 
 SBLAS_API int sblas_plan_build_rowblocks_on(int gpu, int is_f64, sblasPlan_t plan, const int32_t* d_colidx,
                                             const void* d_val);
 SBLAS_API int sblas_scal_add_on(int gpu, int is_f64, void* d_v, double val, double beta, int64_t n);
+/* CsrToCsc / CscToCsr (matrix.h:40-91) and CooSparseMatrix::sortByRow (matrix.h:221-237) on a logical
+ * GPU's default stream.  (m, n, d_ptr, d_idx) = (rows, cols, rowptr, colidx) for CSR -> CSC and
+ * (cols, rows, colptr, rowidx) for CSC -> CSR. */
+SBLAS_API int sblas_compressed_transpose_on(int gpu, int is_f64, int32_t m, int32_t n, int64_t nnz,
+                                            const int32_t* d_ptr, const int32_t* d_idx, const void* d_val,
+                                            int32_t* d_out_ptr, int32_t* d_out_idx, void* d_out_val);
+SBLAS_API int sblas_coo_sort_on(int gpu, int is_f64, int64_t nnz, int32_t height, int32_t* d_row, int32_t* d_col,
+                                void* d_val);
 /* DenseMatrix::sync2gpu / sync2cpu for one GPU's slice (matrix.h:541-570, :595-612).  h is the
  * host slice: `dim` leading-dimension lines of `second` contiguous elements each (for the
  * col_major operands of SpMM: dim columns of `second` rows).  dev_layout SBLAS_COL_MAJOR keeps

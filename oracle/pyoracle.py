@@ -173,6 +173,37 @@ class Oracle(_Base):
         return m.value, n.value, rp, ci, v
 
 
+    def csr2csc(self, m, n, rp, ci, v):
+        """matrix.h:40-64 -> (cscColPtr, cscRowIdx, cscVal)"""
+        rp, ci = _i32(rp), _i32(ci)
+        nnz = len(ci)
+        cp = np.zeros(n + 1, np.int32)
+        ri = np.zeros(max(nnz, 1), np.int32)[:nnz]
+        cv = np.zeros(max(nnz, 1), v.dtype)[:nnz]
+        self._f("csr2csc_" + _sfx(v.dtype))(C.c_int(m), C.c_int(n), C.c_int(nnz), _p(rp), _p(ci), _p(v), _p(ri),
+                                            _p(cp), _p(cv))
+        return cp, ri, cv
+
+    def csc2csr(self, n, m, cp, ri, v):
+        """matrix.h:67-91 -> (csrRowPtr, csrColIdx, csrVal); the same loop with the roles exchanged"""
+        if self.prefix == "ref_":
+            assert v.dtype == np.float64
+            cp, ri = _i32(cp), _i32(ri)
+            nnz = len(ri)
+            rp = np.zeros(m + 1, np.int32)
+            ci = np.zeros(max(nnz, 1), np.int32)[:nnz]
+            cv = np.zeros(max(nnz, 1), v.dtype)[:nnz]
+            self._f("csc2csr_f64")(C.c_int(n), C.c_int(m), C.c_int(nnz), _p(cp), _p(ri), _p(v), _p(ci), _p(rp), _p(cv))
+            return rp, ci, cv
+        return self.csr2csc(n, m, cp, ri, v)
+
+    def coo_sort(self, r, c, v):
+        """matrix.h:221-237 (stable restatement) -> sorted copies"""
+        r, c, v = _i32(r).copy(), _i32(c).copy(), np.ascontiguousarray(v, np.float64).copy()
+        self._f("coo_sort_f64")(C.c_long(len(r)), _p(r), _p(c), _p(v))
+        return r, c, v
+
+
 class Reference(Oracle):
     """The reference's own code (oracle/ref_shim.cu).  Same methods; differences:
     spmv needs square A (spmv.h:21); spmm only with Bh=w, Ch=h; no *_rows_omp."""

@@ -141,6 +141,20 @@ int ref_mtx_info(const char* fn, int* m, int* n, int* nnz, int* sym) {
 }
 int ref_mtx_data(const char* fn, int* rp, int* ci, double* v) { return mmio_data(rp, ci, v, fn); }
 
+// matrix.h:40-64 and :67-91, the reference's own templates (plain CPU code)
+void ref_csr2csc_f64(int m, int n, int nnz, const int* rp, const int* ci, const double* v, int* cscRowIdx,
+                     int* cscColPtr, double* cscVal) {
+  CsrToCsc<int, double>(m, n, nnz, rp, ci, v, cscRowIdx, cscColPtr, cscVal);
+}
+void ref_csr2csc_f32(int m, int n, int nnz, const int* rp, const int* ci, const float* v, int* cscRowIdx,
+                     int* cscColPtr, float* cscVal) {
+  CsrToCsc<int, float>(m, n, nnz, rp, ci, v, cscRowIdx, cscColPtr, cscVal);
+}
+void ref_csc2csr_f64(int n, int m, int nnz, const int* cp, const int* ri, const double* v, int* csrColIdx,
+                     int* csrRowPtr, double* csrVal) {
+  CscToCsr<int, double>(n, m, nnz, cp, ri, v, csrColIdx, csrRowPtr, csrVal);
+}
+
 // utility.h:182-191
 int ref_check_equal_f64(const double* x, const double* y, size_t m) { return check_equal<double>(x, y, m); }
 int ref_check_equal_f32(const float* x, const float* y, size_t m) { return check_equal<float>(x, y, m); }

@@ -293,6 +293,51 @@ ORACLE_API int oracle_mtx_data(const char* fn, int* rp, int* ci, double* v) {
   return 0;
 }
 
+/* ---- format conversion --------------------------------------------------------
+ * matrix.h:40-64 CsrToCsc: column histogram, exclusive scan (utility.h:276-288), then the entries
+ * are dropped into their columns in ROW order, so a column keeps CSR order.  CscToCsr
+ * (matrix.h:67-91) is the same loop with rows and columns exchanged: call this with (n, m, colptr,
+ * rowidx, ...). */
+#define ORACLE_CSR2CSC(SFX, T)                                                                          \
+  ORACLE_API void oracle_csr2csc_##SFX(int m, int n, int nnz, const int* rp, const int* ci, const T* v, \
+                                       int* cscRowIdx, int* cscColPtr, T* cscVal) {                     \
+    memset(cscColPtr, 0, sizeof(int) * ((size_t)n + 1));                                                \
+    for (int i = 0; i < nnz; i++) cscColPtr[ci[i]]++;                                                   \
+    int run = 0;                                                                                        \
+    for (int c = 0; c <= n; c++) { int t = cscColPtr[c]; cscColPtr[c] = run; run += t; }                \
+    int* incr = (int*)malloc(sizeof(int) * ((size_t)n + 1));                                            \
+    memcpy(incr, cscColPtr, sizeof(int) * ((size_t)n + 1));                                             \
+    for (int row = 0; row < m; row++)                                                                   \
+      for (int j = rp[row]; j < rp[row + 1]; j++) {                                                     \
+        int col = ci[j];                                                                                \
+        cscRowIdx[incr[col]] = row;                                                                     \
+        cscVal[incr[col]] = v[j];                                                                       \
+        incr[col]++;                                                                                    \
+      }                                                                                                 \
+    free(incr);                                                                                         \
+  }
+ORACLE_CSR2CSC(f64, double)
+ORACLE_CSR2CSC(f32, float)
+
+/* matrix.h:221-237 sortByRow: qsort of (row, col, val) records with cmp_func (matrix.h:100-115), which
+ * orders by (row, col) and calls equal pairs equal — their relative order is whatever qsort does.
+ * Restated as a STABLE merge sort by (row, col) (equal pairs keep input order), the one well-defined
+ * choice; identical to the reference wherever (row, col) pairs are distinct. */
+typedef struct { int r, c; double v; long pos; } oracle_coo_t;
+static int oracle_coo_cmp(const void* a, const void* b) {
+  const oracle_coo_t *x = (const oracle_coo_t*)a, *y = (const oracle_coo_t*)b;
+  if (x->r != y->r) return x->r > y->r ? 1 : -1;
+  if (x->c != y->c) return x->c > y->c ? 1 : -1;
+  return x->pos > y->pos ? 1 : (x->pos < y->pos ? -1 : 0);
+}
+ORACLE_API void oracle_coo_sort_f64(long nnz, int* r, int* c, double* v) {
+  oracle_coo_t* a = (oracle_coo_t*)malloc(sizeof(oracle_coo_t) * (size_t)(nnz > 0 ? nnz : 1));
+  for (long i = 0; i < nnz; i++) { a[i].r = r[i]; a[i].c = c[i]; a[i].v = v[i]; a[i].pos = i; }
+  qsort(a, (size_t)nnz, sizeof(oracle_coo_t), oracle_coo_cmp);
+  for (long i = 0; i < nnz; i++) { r[i] = a[i].r; c[i] = a[i].c; v[i] = a[i].v; }
+  free(a);
+}
+
 ORACLE_API int oracle_max_threads(void) {
 #ifdef _OPENMP
   return omp_get_max_threads();

@@ -312,6 +312,42 @@ int sblas_mtx_info(const char* fn, int32_t* m, int32_t* n, int32_t* nnz, int32_t
   return 0;
 }
 
+int sblas_mtx_coo_info(const char* fn, int32_t* m, int32_t* n, int32_t* nz) {
+  std::lock_guard<std::mutex> lk(g_mtx_cache.mu);
+  Mtx& M = g_mtx_cache.M;
+  g_mtx_cache.valid = false;
+  M = Mtx();
+  int rc = load_mtx(fn, M);
+  if (rc) return rc;
+  g_mtx_cache.key = mtx_key(fn);
+  g_mtx_cache.valid = !g_mtx_cache.key.empty();
+  if (m) *m = M.m;
+  if (n) *n = M.n;
+  if (nz) *nz = (int32_t)M.ri.size();
+  return 0;
+}
+
+int sblas_mtx_coo_data(const char* fn, int32_t* rowidx, int32_t* colidx, double* val) {
+  std::lock_guard<std::mutex> lk(g_mtx_cache.mu);
+  Mtx local;
+  Mtx* pM = &local;
+  if (g_mtx_cache.valid && g_mtx_cache.key == mtx_key(fn)) {
+    pM = &g_mtx_cache.M;
+  } else {
+    int rc = load_mtx(fn, local);
+    if (rc) return rc;
+  }
+  const size_t nz = pM->ri.size();
+  if (nz) {
+    memcpy(rowidx, pM->ri.data(), nz * sizeof(int32_t));
+    memcpy(colidx, pM->cj.data(), nz * sizeof(int32_t));
+    memcpy(val, pM->v.data(), nz * sizeof(double));
+  }
+  g_mtx_cache.valid = false;
+  g_mtx_cache.M = Mtx();
+  return 0;
+}
+
 int sblas_mtx_data(const char* fn, int32_t* rowptr, int32_t* colidx, double* val) {
   std::lock_guard<std::mutex> lk(g_mtx_cache.mu);
   Mtx local;

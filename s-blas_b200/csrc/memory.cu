@@ -199,6 +199,21 @@ int sblas_plan_build_rowblocks_on(int gpu, int is_f64, sblasPlan_t plan, const i
   return is_f64 ? sblas_plan_build_rowblocks_f64(nullptr, plan, d_colidx, (const double*)d_val, 0)
                 : sblas_plan_build_rowblocks_f32(nullptr, plan, d_colidx, (const float*)d_val, 0);
 }
+// CsrToCsc / CscToCsr / sortByRow (matrix.h:40-91, :221-237) on a logical GPU's default stream; for
+// transpose_on, (m, n, ptr, idx) are (rows, cols, rowptr, colidx) for CSR -> CSC and (cols, rows,
+// colptr, rowidx) for CSC -> CSR.
+int sblas_compressed_transpose_on(int gpu, int is_f64, int32_t m, int32_t n, int64_t nnz, const int32_t* d_ptr,
+                                  const int32_t* d_idx, const void* d_val, int32_t* d_out_ptr, int32_t* d_out_idx,
+                                  void* d_out_val) {
+  SBLAS_ON_GPU(gpu);
+  return is_f64 ? sblas_csr2csc_f64(nullptr, m, n, nnz, d_ptr, d_idx, (const double*)d_val, d_out_ptr, d_out_idx, (double*)d_out_val)
+                : sblas_csr2csc_f32(nullptr, m, n, nnz, d_ptr, d_idx, (const float*)d_val, d_out_ptr, d_out_idx, (float*)d_out_val);
+}
+int sblas_coo_sort_on(int gpu, int is_f64, int64_t nnz, int32_t height, int32_t* d_row, int32_t* d_col, void* d_val) {
+  SBLAS_ON_GPU(gpu);
+  return is_f64 ? sblas_coo_sort_f64(nullptr, nnz, height, d_row, d_col, (double*)d_val)
+                : sblas_coo_sort_f32(nullptr, nnz, height, d_row, d_col, (float*)d_val);
+}
 int sblas_scal_add_on(int gpu, int is_f64, void* d_v, double val, double beta, int64_t n) {
   SBLAS_ON_GPU(gpu);
   return is_f64 ? sblas_scal_add_f64(nullptr, (double*)d_v, val, beta, n)

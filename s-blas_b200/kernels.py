@@ -88,6 +88,53 @@ def read_mtx(path, threads=None):
     return m.value, n.value, rp, ci, v
 
 
+def read_mtx_coo(path, threads=None):
+    """The coordinate entries as the file holds them (CooSparseMatrix(const char*), matrix.h:142-176):
+    -> (h, w, row, col, val[f64]), 0-based, file order, no symmetric expansion."""
+    lib().sblas_mtx_set_threads(C.c_int(int(threads or 0)))
+    m, n, nz = C.c_int32(), C.c_int32(), C.c_int32()
+    check(lib().sblas_mtx_coo_info(path.encode(), C.byref(m), C.byref(n), C.byref(nz)), "mtx_coo_info")
+    r = np.zeros(nz.value, np.int32)
+    c = np.zeros(nz.value, np.int32)
+    v = np.zeros(nz.value, np.float64)
+    check(lib().sblas_mtx_coo_data(path.encode(), vp(r), vp(c), vp(v)), "mtx_coo_data")
+    return m.value, n.value, r, c, v
+
+
+# ---- format conversion on the device (matrix.h:40-91, :221-237) -------------------------------------
+def csr2csc(m, n, rowptr, colidx, val, stream=None):
+    """CsrToCsc (matrix.h:40-64) on device tensors -> (cscColPtr, cscRowIdx, cscVal)."""
+    import torch
+    nnz = val.numel()
+    cp = torch.empty(n + 1, dtype=torch.int32, device=val.device)
+    ri = torch.empty(nnz, dtype=torch.int32, device=val.device)
+    cv = torch.empty(nnz, dtype=val.dtype, device=val.device)
+    fn = getattr(lib(), "sblas_csr2csc_" + _sfx(val.dtype))
+    check(fn(stream_ptr(stream), C.c_int32(m), C.c_int32(n), C.c_int64(nnz), vp(rowptr), vp(colidx), vp(val),
+             vp(cp), vp(ri), vp(cv)), "csr2csc")
+    return cp, ri, cv
+
+
+def csc2csr(n, m, colptr, rowidx, val, stream=None):
+    """CscToCsr (matrix.h:67-91; the reference's argument order n, m) -> (csrRowPtr, csrColIdx, csrVal)."""
+    import torch
+    nnz = val.numel()
+    rp = torch.empty(m + 1, dtype=torch.int32, device=val.device)
+    ci = torch.empty(nnz, dtype=torch.int32, device=val.device)
+    cv = torch.empty(nnz, dtype=val.dtype, device=val.device)
+    fn = getattr(lib(), "sblas_csc2csr_" + _sfx(val.dtype))
+    check(fn(stream_ptr(stream), C.c_int32(n), C.c_int32(m), C.c_int64(nnz), vp(colptr), vp(rowidx), vp(val),
+             vp(rp), vp(ci), vp(cv)), "csc2csr")
+    return rp, ci, cv
+
+
+def coo_sort(height, row, col, val, stream=None):
+    """CooSparseMatrix::sortByRow (matrix.h:221-237), in place on device tensors, stable."""
+    fn = getattr(lib(), "sblas_coo_sort_" + _sfx(val.dtype))
+    check(fn(stream_ptr(stream), C.c_int64(val.numel()), C.c_int32(height), vp(row), vp(col), vp(val)), "coo_sort")
+    return row, col, val
+
+
 # ---- plan -------------------------------------------------------------------------------------------
 class Plan:
     """Per-device CSR plan (row statistics + tile tables).  Keeps the rowptr tensor alive."""

@@ -146,3 +146,17 @@ def test_reference_own_drivers_on_our_headers(n_gpu):
         assert "Validation = True" in r.stdout, (method, r.stdout + r.stderr)
     r = _run([os.path.join(REFDRV, "refdrv_spmv_test_um"), ASH, "1.0", "1.0", str(n_gpu)], _devmap())
     assert "Validation = True" in r.stdout, r.stdout + r.stderr
+
+
+@pytest.mark.gpu
+def test_reference_own_unit_test_on_our_headers():
+    """The reference's unmodified unit_test.cu (COO / CSR / CSC / dense containers, then SpMM method 1 and 2 and
+    SpMV with k=256, alpha=3, beta=4 on 4 GPUs, unit_test.cu:176-187) built against include/."""
+    exe = os.path.join(REFDRV, "refdrv_unit_test")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/refdrv_unit_test not built (needs /root/reference at build time)")
+    env = dict(os.environ, SBLAS_DEVICE_MAP=_devmap())
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=600, env=env, cwd=os.path.dirname(ASH))
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert r.stdout.count("Validation = True") == 3 and "Validation = False" not in r.stdout, r.stdout + r.stderr
+    assert "Building csc matrix from a csr matrix." in r.stdout

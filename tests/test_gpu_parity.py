@@ -455,3 +455,64 @@ def test_synth_generators_match_numpy(sblas, dev, dtype):
         for g, r in zip(got[2:], ref):
             assert np.array_equal(g.cpu().numpy(), r)
     assert S.laplace2d(2048, 2048, td, dev)[4].numel() == 20963328
+
+
+# ------------------------------------------------------ format containers ----
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+@pytest.mark.parametrize("shape", [(1, 1, 1), (300, 200, 5), (50, 40000, 30), (20000, 64, 3), (4000, 4000, 0.01)])
+def test_csr2csc_bit_identical(sblas, dev, oracle, dtype, shape):
+    """CsrToCsc / CscToCsr on the device == the reference's CPU loops (matrix.h:40-91), bit for bit: empty rows
+    and columns, unsorted rows, duplicate (row, col) pairs."""
+    import torch
+    K = sblas.kernels
+    m, n, avg = shape
+    rng = np.random.default_rng(m + n)
+    lens = rng.poisson(avg, m) * (rng.random(m) > 0.2)
+    rp = np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)
+    ci = rng.integers(0, n, rp[-1]).astype(np.int32)
+    v = rng.standard_normal(rp[-1]).astype(dtype)
+    ref = oracle.csr2csc(m, n, rp, ci, v)
+    drp, dci, dv = (_t(dev, a) for a in (rp, ci, v))
+    got = K.csr2csc(m, n, drp, dci, dv)
+    torch.cuda.synchronize()
+    for g, r in zip(got, ref):
+        assert np.array_equal(g.cpu().numpy(), r)
+    back = K.csc2csr(n, m, *got)
+    ref2 = oracle.csc2csr(n, m, *ref)
+    for g, r in zip(back, ref2):
+        assert np.array_equal(g.cpu().numpy(), r)
+    assert np.array_equal(back[0].cpu().numpy(), rp)
+
+
+@pytest.mark.gpu
+def test_csr2csc_config_sizes(sblas, dev):
+    """At BASELINE size (config 2: 4M rows, 21M nnz): CSR -> CSC -> CSR returns the input (its rows are sorted),
+    and the CSC of the symmetric Laplacian pattern equals its CSR."""
+    import torch
+    K = sblas.kernels
+    rows, cols, rp, ci, v = sblas.synth.laplace2d(2048, 2048, torch.float64, dev)
+    cp, ri, cv = K.csr2csc(rows, cols, rp, ci, v)
+    assert torch.equal(cp, rp) and torch.equal(ri, ci) and torch.equal(cv, v)   # A = A^T, sorted rows
+    rp2, ci2, v2 = K.csc2csr(cols, rows, cp, ri, cv)
+    assert torch.equal(rp2, rp) and torch.equal(ci2, ci) and torch.equal(v2, v)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_coo_sort_and_loader(sblas, dev, oracle, golden, dtype):
+    """CooSparseMatrix(const char*) (matrix.h:142-237): entries as the file holds them, then sorted by (row, col)."""
+    import torch
+    K = sblas.kernels
+    h, w, r, c, v = K.read_mtx_coo(golden["ash85_path"])
+    assert (h, w, len(r)) == (85, 85, 304)          # stored entries of the symmetric file, not expanded
+    rng = np.random.default_rng(9)
+    r = np.concatenate([r, rng.integers(0, h, 5000).astype(np.int32)])
+    c = np.concatenate([c, rng.integers(0, w, 5000).astype(np.int32)])
+    v = rng.standard_normal(len(r)).astype(dtype)
+    rs, cs, vs = oracle.coo_sort(r, c, v.astype(np.float64))
+    dr, dc, dv = (_t(dev, a) for a in (r, c, v))
+    K.coo_sort(h, dr, dc, dv)
+    torch.cuda.synchronize()
+    assert np.array_equal(dr.cpu().numpy(), rs) and np.array_equal(dc.cpu().numpy(), cs)
+    assert np.array_equal(dv.cpu().numpy(), vs.astype(dtype))

@@ -143,3 +143,30 @@ def test_against_reference_bitexact(oracle, reference):
                     assert oracle.find_row(rp, int(idx)) == reference.find_row(rp, int(idx))
     assert np.array_equal(oracle.rand_fill(1000), reference.rand_fill(1000))
     assert np.array_equal(oracle.rand_fill(1000, np.float32), reference.rand_fill(1000, np.float32))
+
+
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_format_conversion_against_reference(oracle, reference, dtype):
+    """the restated CsrToCsc / CscToCsr (matrix.h:40-91) against the reference's own templates,
+    with empty rows and columns, unsorted rows and duplicate (row, col) pairs."""
+    rng = np.random.default_rng(5)
+    for m, n, avg in ((1, 1, 1), (60, 45, 6), (200, 900, 3), (500, 20, 12)):
+        lens = rng.poisson(avg, m) * (rng.random(m) > 0.2)
+        rp = np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)
+        ci = rng.integers(0, n, rp[-1]).astype(np.int32)
+        v = rng.standard_normal(rp[-1]).astype(dtype)
+        a, b = oracle.csr2csc(m, n, rp, ci, v), reference.csr2csc(m, n, rp, ci, v)
+        assert all(np.array_equal(x, y) for x, y in zip(a, b))
+        if dtype == np.float64:
+            a2, b2 = oracle.csc2csr(n, m, *a), reference.csc2csr(n, m, *b)
+            assert all(np.array_equal(x, y) for x, y in zip(a2, b2))
+            assert np.array_equal(a2[0], rp)
+
+
+def test_coo_sort_restatement(oracle):
+    rng = np.random.default_rng(6)
+    r, c = rng.integers(0, 30, 2000).astype(np.int32), rng.integers(0, 30, 2000).astype(np.int32)
+    v = rng.standard_normal(2000)
+    rs, cs, vs = oracle.coo_sort(r, c, v)
+    o = np.lexsort((c, r))   # stable: equal (row, col) pairs keep input order
+    assert np.array_equal(rs, r[o]) and np.array_equal(cs, c[o]) and np.array_equal(vs, v[o])
