@@ -240,7 +240,8 @@ def run_ours(args, wl_key):
         torch.cuda.empty_cache()
         ld = k
         xB = pkg.synth.fill_uniform(torch.empty(cols * ld, dtype=tdtype, device=dev), stream_id=11)
-        stitch = args.stitch
+        stitch = D.choose_stitch(rb, world) if args.stitch == "auto" else args.stitch
+        cfg_extra["stitch_requested"] = args.stitch
         peer_ptrs, ipc = None, None
         mc_ptr = 0
         if stitch == "mc":
@@ -258,7 +259,7 @@ def run_ours(args, wl_key):
         else:
             yC = torch.ones(rows * ld, dtype=tdtype, device=dev)
         opx = D.RowSplitOp(rows, cols, rb, lrp, lci, lv, k=k, ld=ld if op == "spmm" else 1,
-                           stitch=stitch, peer_ptrs=peer_ptrs, mc_ptr=mc_ptr)
+                           stitch=stitch, peer_ptrs=peer_ptrs, mc_ptr=mc_ptr, flags=args.flags)
 
         def step_compute():
             opx.compute(xB, yC, 1.0, 1.0)
@@ -709,7 +710,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=None, choices=list(WORKLOADS))
     ap.add_argument("--scaling", default=None, choices=["weak", "strong"])
-    ap.add_argument("--stitch", default="peer", choices=["peer", "nccl", "mc"])
+    ap.add_argument("--stitch", default="auto", choices=["auto", "peer", "nccl", "mc"],
+                    help="auto: peer stores, multicast stores when the row panels are very unequal (dist.choose_stitch)")
     ap.add_argument("--variant", type=int, default=0)
     ap.add_argument("--tile", type=int, default=0)
     ap.add_argument("--lanes", type=int, default=0)

@@ -115,6 +115,17 @@ class SymmBuffer:
         return self.t
 
 
+def choose_stitch(row_begin, world):
+    """The stitch for replicated y / C when the caller does not name one.  In-kernel peer stores are the
+    fastest when the panels hold similar numbers of rows (every GPU sends (n-1) x its panel).  nnz-balanced
+    panels of a skewed matrix do not: the GPU that owns the long sparse tail sends several times the mean,
+    and its NVLink egress sets the step (R-MAT config 4, 8 GPUs: one panel holds 43 % of the rows, 0.312 ms).
+    NVSwitch multicast stores send each panel ONCE and let the switch replicate it (0.172 ms)."""
+    rows = [int(row_begin[i + 1]) - int(row_begin[i]) for i in range(world)]
+    mean = max(sum(rows) / max(world, 1), 1.0)
+    return "mc" if world >= 4 and max(rows) > 2.0 * mean else "peer"
+
+
 class RowSplitOp:
     """y/C <- beta*y/C + alpha*A*x/B with A split into row panels across the ranks.
 
@@ -123,7 +134,7 @@ class RowSplitOp:
     view of an IpcBuffer whose peers have been opened (pass peer_ptrs)."""
 
     def __init__(self, rows_total, cols, row_begin, rp, ci, val, k=1, ld=1, stitch="nccl",
-                 peer_ptrs=None, plan=None, mc_ptr=0):
+                 peer_ptrs=None, plan=None, mc_ptr=0, flags=0):
         dist = _dist()
         self.rank = dist.get_rank() if dist.is_initialized() else 0
         self.world = dist.get_world_size() if dist.is_initialized() else 1
@@ -135,21 +146,21 @@ class RowSplitOp:
             self.plan.build_rowblocks(ci, val)      # SpMM: row-block mirror when it pays (sync2gpu work)
         self.stitch = stitch if self.world > 1 else "none"
         self.equal = len({self.row_begin[i + 1] - self.row_begin[i] for i in range(self.world)}) == 1
-        self.opts = None
+        self.opts = make_opts(flags=flags) if flags else None   # extra SBLAS_FLAG_* for the kernels (experiments)
         self.flags = None
         if self.stitch == "mc":
             # one store per finished row slice into the multicast address: the NVSwitch replicates it
             # into every rank's buffer (this rank's included), so a GPU sends |panel| bytes, not (n-1)x
             if not mc_ptr:
                 raise RuntimeError("stitch='mc' needs a multicast address (SymmBuffer.mc_ptr is 0 on this box)")
-            self.opts = make_opts(replicas=[mc_ptr + self.r0 * ld * val.element_size()])
+            self.opts = make_opts(replicas=[mc_ptr + self.r0 * ld * val.element_size()], flags=flags)
             self.stitch = "peer"            # same device-side barrier closes the step
             peer_ptrs = None
         elif self.stitch == "peer":
             esz = val.element_size()
             off = self.r0 * ld * esz
             reps = [p + off for r, p in enumerate(peer_ptrs) if r != self.rank]
-            self.opts = make_opts(replicas=reps)
+            self.opts = make_opts(replicas=reps, flags=flags)
         if self.stitch == "peer":
             # flag words of the device-side barrier that completes the step (sblas_peer_barrier)
             import torch

@@ -249,3 +249,13 @@ def test_python_mirror_api_surface(sblas):
     for f in ("csrRowPtr", "csrColIdx", "csrVal", "csrRowPtr_gpu", "csrColIdx_gpu", "csrVal_gpu",
               "nnz_gpu", "starting_row_gpu", "stoping_row_gpu", "n_gpu", "policy"):
         assert hasattr(A, f)
+
+
+def test_choose_stitch(sblas):
+    """dist.choose_stitch: peer stores for even row panels, multicast for the skewed panels of a power-law input."""
+    D = sblas.dist
+    assert D.choose_stitch([0, 100, 200, 300, 400], 4) == "peer"
+    assert D.choose_stitch([0, 10, 20], 2) == "peer"                      # two GPUs: nothing to replicate by switch
+    c4_panels = [38929, 223252, 327772, 594328, 983560, 1527264, 1056772, 3636731]   # R-MAT config 4, 8 GPUs
+    rb = np.concatenate([[0], np.cumsum(c4_panels)])
+    assert D.choose_stitch(rb, 8) == "mc"
