@@ -78,6 +78,8 @@ enum {
   SBLAS_FLAG_NO_PREFETCH_B = 32, /* ... never */
   SBLAS_FLAG_SPLIT_SERIAL = 128, /* SBLAS_SPMV_SPLIT: row pointers loaded before the A stream and y read in the
                                    epilogue (the first version; four dependent memory round trips per CTA) */
+  SBLAS_FLAG_PREFETCH_C = 512,  /* SBLAS_SPMM_ROWBLOCK_PIPE: consumer warps prefetch the old C rows of the tile two
+                                   ahead into L2 */
   SBLAS_FLAG_SPLIT_SEG = 256,   /* SBLAS_SPMV_SPLIT: phase 2 as an in-place segmented sum (row-start bitmap,
                                    reverse segmented scan of the thread leads), balanced for any row mix */
   SBLAS_FLAG_SPLIT_MERGE = 64   /* SBLAS_SPMV_SPLIT: balanced merge-path walk in phase 2 (every thread owns

@@ -17,6 +17,7 @@ FLAG_PREFETCH_B, FLAG_NO_PREFETCH_B = 16, 32
 FLAG_SPLIT_MERGE = 64
 FLAG_SPLIT_SERIAL = 128
 FLAG_SPLIT_SEG = 256
+FLAG_PREFETCH_C = 512
 ROW_MAJOR, COL_MAJOR = 0, 1
 
 

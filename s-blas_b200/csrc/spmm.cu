@@ -405,6 +405,8 @@ __device__ __forceinline__ void rbp_blocks(uint32_t a_cm, uint32_t a_val, int n,
   }
 }
 
+constexpr int kRbpCPrefetchDist = 2;  // tiles ahead for the L2 prefetch of old C rows (SBLAS_FLAG_PREFETCH_C)
+
 template <typename T, int VEC, int NB, int R, bool EXACT, int NSTAGE>
 __global__ void __launch_bounds__(kRbpBlock, (R == 4 ? 4 : 3) - NB)
 spmm_rbp_kernel(int64_t n_blockrows, const int32_t* __restrict__ blk_ptr, const int2* __restrict__ colmask,
@@ -469,7 +471,7 @@ spmm_rbp_kernel(int64_t n_blockrows, const int32_t* __restrict__ blk_ptr, const 
       if (lane == 1 && p1 > m1) cp_async8(s_cm + (m1 - p0a), colmask + m1);   // tail (1 entry)
       if (lane >= 2 && lane < 2 + nbr + 1) cp_async4(s_ptr + (lane - 2), blk_ptr + br0 + (lane - 2));
       cp_async_mbar_arrive_noinc(&full[s]);
-      if (prefetch) {
+      if (prefetch & 1) {
         // the B rows this tile will gather: pull them into L1 while the consumers are still on
         // the previous tile (first touches come from HBM, nobody else prefetches them).
         // (cp.async.bulk.prefetch.L2 per row instead: 12.5 ms against 9.3 ms without, TMA-bound.)
@@ -506,6 +508,21 @@ spmm_rbp_kernel(int64_t n_blockrows, const int32_t* __restrict__ blk_ptr, const 
     const uint32_t st_a = stages_a + (uint32_t)s * (uint32_t)stage_bytes;
     mbar_wait(&full[s], (uint32_t)(i / NSTAGE) & 1u);
     const int64_t br = (tile0 + i) * W + w;
+    if ((prefetch & 2) && i + kRbpCPrefetchDist < my_tiles) {
+      // the old C rows this warp will need kRbpCPrefetchDist tiles from now: into L2 today, so that the
+      // LDGSTS at the top of that tile returns in an L2 round trip and not a DRAM one (the block loop of one
+      // tile is shorter than the loaded DRAM latency, so the C fetch was exposed at every epilogue)
+      const int64_t brn = br + (int64_t)kRbpCPrefetchDist * W;
+      if (brn < n_blockrows) {
+        const int lines = (NB * 32 * VEC * (int)sizeof(T) + 127) / 128;   // 128-byte lines per row slice
+        for (int idx = lane; idx < R * lines; idx += 32) {
+          const int r = idx / lines, ln = idx - r * lines;
+          const int64_t row = brn * R + r;
+          const int c0 = p * NB * 32 * VEC + ln * (128 / (int)sizeof(T));
+          if (row < sink.rows && c0 < kp) prefetch_l2(sink.C + row * sink.ldc + c0);
+        }
+      }
+    }
     if (br < n_blockrows) {
       const int32_t p0a = lds_i1(st_a + off_ptr) & ~1;
       const int2 bp = make_int2(lds_i1(st_a + off_ptr + w * 4), lds_i1(st_a + off_ptr + w * 4 + 4));
@@ -596,8 +613,9 @@ static int launch_rbp_r(cudaStream_t st, const sblasPlan_st* plan, int NB, int l
   const int2* cm = (const int2*)rb.d_colmask;
   const T* bv = (const T*)rb.d_val;
   const uint32_t ldb_bytes = (uint32_t)(ldb * (int64_t)sizeof(T));
-  const int32_t prefetch = (sink.flags & SBLAS_FLAG_NO_PREFETCH_B) ? 0
-                           : ((sink.flags & SBLAS_FLAG_PREFETCH_B) || (NB <= 1 && logP == 0)) ? 1 : 0;
+  const int32_t prefetch = ((sink.flags & SBLAS_FLAG_NO_PREFETCH_B) ? 0
+                            : ((sink.flags & SBLAS_FLAG_PREFETCH_B) || (NB <= 1 && logP == 0)) ? 1 : 0) |
+                           ((sink.flags & SBLAS_FLAG_PREFETCH_C) ? 2 : 0);
   void* args[] = {(void*)&rb.n_blockrows, (void*)&rb.d_ptr, (void*)&cm, (void*)&bv, (void*)&B, (void*)&ldb_bytes,
                   (void*)&sink, (void*)&cap_blocks, (void*)&kp, (void*)&logP, (void*)&prefetch};
   SBLAS_CUDA(cudaLaunchKernel(kern, dim3(grid), dim3(kRbpBlock), args, smem, st));
