@@ -1054,6 +1054,11 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
                            : (vec ? spmv_merge_kernel<T, kSpmvBlock, true> : spmv_merge_kernel<T, kSpmvBlock, false>);
         if (flags & SBLAS_FLAG_SPLIT_SEG)
           kern = vec ? spmv_split_seg_kernel<T, kSpmvBlock, true> : spmv_split_seg_kernel<T, kSpmvBlock, false>;
+        {  // experiment hook: SBLAS_SPLIT_CARVEOUT=<percent of the 256 KB given to shared memory>; the driver's
+           // default takes whatever makes the most CTAs resident, which can leave almost no L1 (tile >= 3072)
+          static const int carve = [] { const char* e = getenv("SBLAS_SPLIT_CARVEOUT"); return e ? atoi(e) : -1; }();
+          if (carve >= 0) cudaFuncSetAttribute((const void*)kern, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+        }
         if ((rc = set_smem_once<T>((const void*)kern, smem)) == 0) {
           kern<<<tt->n_tiles, kSpmvBlock, smem, st>>>(tt->d_tile_row, tile, rows, nnz, rp, ci, v, x,
                                                       sink, carry_out, head_val, head_row, cap);

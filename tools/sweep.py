@@ -53,7 +53,7 @@ def main():
         grid = [dict(variant=0)]
         grid += [dict(variant=pkg.SPMV_TILE, tile=t, lanes=l) for t in (1024, 1536, 2048, 3072, 4096, 6144, 8192)
                  for l in ((0,) if args.grid == "default" else (0, 1, 2, 4, 8, 16, 32))]
-        grid += [dict(variant=pkg.SPMV_SPLIT, tile=t, flags=f) for t in (768, 1024, 1536, 2048, 2560) for f in (0, pkg.FLAG_SPLIT_SEG)]
+        grid += [dict(variant=pkg.SPMV_SPLIT, tile=t, flags=f) for t in (1536, 2048, 3072, 4096, 6144) for f in (0,)]
         grid += [dict(variant=pkg.SPMV_PIPE, tile=t, stages=st, lanes=l) for t in (1536, 2048, 3072, 4096, 6144, 8192) for st in (2, 3, 4)
                  for l in ((0,) if args.grid == 'default' else (0, 1, 2, 4, 8, 16))]
         grid += [dict(variant=pkg.SPMV_VECTOR, lanes=l, flags=f) for l in (1, 2, 4, 8, 16, 32) for f in (0, 1)]
