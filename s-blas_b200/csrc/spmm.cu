@@ -603,9 +603,15 @@ static int launch_rbp_r(cudaStream_t st, const sblasPlan_st* plan, int NB, int l
   const size_t smem = smem_for(ns);
   SBLAS_CHECK(smem <= 200 * 1024, "spmm rowblock pipe: tile needs %zu bytes of shared memory", smem);
   if (smem > 48 * 1024) SBLAS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  // experiment hooks: SBLAS_RBP_CARVEOUT = percent of the 256 KB L1/shared array given to shared memory,
+  // SBLAS_RBP_PER_SM = resident CTAs per SM the persistent grid is sized for
+  static const int env_carve = [] { const char* e = getenv("SBLAS_RBP_CARVEOUT"); return e ? atoi(e) : -1; }();
+  static const int env_per_sm = [] { const char* e = getenv("SBLAS_RBP_PER_SM"); return e ? atoi(e) : 0; }();
+  if (env_carve >= 0) cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, env_carve);
   int per_sm = 0;
   SBLAS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kRbpBlock, smem));
   SBLAS_CHECK(per_sm >= 1, "spmm rowblock pipe: kernel does not fit an SM");
+  if (env_per_sm > 0) per_sm = std::min(per_sm, env_per_sm);
   int n_sm = kNumSM;
   cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, plan->device);
   const int64_t n_tiles = ceil_div(rb.n_blockrows, W);

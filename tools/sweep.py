@@ -62,7 +62,7 @@ def main():
                 for l in ((0,) if args.grid == "default" else (0, 32))]
     if wl['op'] == 'spmm':
         print('rowblocks', plan.build_rowblocks(ci, v, R=args.rb), flush=True)
-        grid = [dict(variant=pkg.SPMM_ROWBLOCK_PIPE, flags=f, stages=st, lanes=P) for f in (0, pkg.FLAG_PREFETCH_C, 1, 1 | pkg.FLAG_PREFETCH_C) for st in (2,) for P in (1,)] + [dict(variant=pkg.SPMM_ROWBLOCK_TILEB, flags=f) for f in (0, 1)] + [dict(variant=pkg.SPMM_ROWBLOCK, flags=f) for f in (0, 1)] + [dict(variant=pkg.SPMM_ROWMAJOR, tile=t, flags=f) for t in (512, 2048) for f in (0, 1)]
+        grid = [dict(variant=pkg.SPMM_ROWBLOCK_PIPE, flags=f, stages=st, lanes=P) for f in (0, 1) for st in (2,) for P in (1,)] + [dict(variant=pkg.SPMM_ROWBLOCK_TILEB, flags=f) for f in (0, 1)] + [dict(variant=pkg.SPMM_ROWBLOCK, flags=f) for f in (0, 1)] + [dict(variant=pkg.SPMM_ROWMAJOR, tile=t, flags=f) for t in (512, 2048) for f in (0, 1)]
     res = []
     if args.only is not None:
         keep = {int(x) for x in str(args.only).split(",")}
