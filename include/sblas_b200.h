@@ -175,6 +175,10 @@ typedef struct sblasCsrStats {
 SBLAS_API int sblas_plan_create_i32(void* stream, int32_t rows, int64_t nnz,
                                     const int32_t* d_rowptr, sblasPlan_t* plan);
 SBLAS_API int sblas_plan_stats(sblasPlan_t plan, sblasCsrStats* out);
+/* Column-locality statistic of the plan: mean |first column of row r+1 - first column of row r| over a row
+ * sample; -1 until an AUTO SpMV with an x larger than L2 measured it.  AUTO takes the sub-warp-per-row kernel
+ * instead of the staged one when it exceeds cols / 256 (uniform-random columns: every gather its own sector). */
+SBLAS_API int sblas_plan_col_jump(sblasPlan_t plan, double* out);
 /* Row-block mirror of A for SpMM ("matrix.h device CSR layout", built inside
  * CsrSparseMatrix::sync2gpu next to the CSR arrays of matrix.h:376-387): R (= 4) consecutive rows
  * form a block row, every distinct column of a block row becomes one block {col, presence mask,

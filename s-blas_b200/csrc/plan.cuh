@@ -66,6 +66,10 @@ struct sblasPlan_st {
   void* d_split_scratch = nullptr;
   size_t split_scratch_bytes = 0;
   sblas::RowBlocks rb;
+  // mean |first column of row r+1 - first column of row r| over a sample of rows (-1 = not measured yet):
+  // ~1 for banded / stencil inputs, ~cols/nnz_per_row for random ones.  Measured lazily by the first AUTO SpMV
+  // whose x does not fit L2 (spmv.cu, col_jump_kernel).
+  double col_jump = -1.0;
 };
 
 namespace sblas {

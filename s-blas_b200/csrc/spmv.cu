@@ -876,6 +876,58 @@ static const void* pipe_kernel_ptr(int stages, int G) {
 #undef SBLAS_PK
 }
 
+// Column locality of consecutive rows, sampled: sum over ~4096 evenly spaced rows r (r and r+1 both non-empty)
+// of |colidx[rowptr[r+1]] - colidx[rowptr[r]]|, and the number of samples.
+__global__ void col_jump_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colidx,
+                                int32_t rows, int32_t n_samples, double* __restrict__ out) {
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  double jump = 0.0, cnt = 0.0;
+  if (s < n_samples) {
+    const int64_t r = (int64_t)s * (rows - 1) / n_samples;
+    if (r + 1 < rows) {
+      const int32_t a0 = rowptr[r], a1 = rowptr[r + 1], a2 = rowptr[r + 2];
+      if (a1 > a0 && a2 > a1) {
+        jump = fabs((double)colidx[a1] - (double)colidx[a0]);
+        cnt = 1.0;
+      }
+    }
+  }
+#pragma unroll
+  for (int m = 16; m > 0; m >>= 1) {
+    jump += __shfl_xor_sync(0xffffffffu, jump, m);
+    cnt += __shfl_xor_sync(0xffffffffu, cnt, m);
+  }
+  if ((threadIdx.x & 31) == 0 && cnt > 0.0) {
+    atomicAdd(out, jump);
+    atomicAdd(out + 1, cnt);
+  }
+}
+
+constexpr size_t kGatherHeavyXBytes = 96u << 20;  // x beyond this does not stay in the 126 MB L2 beside the A stream
+
+// AUTO for gather-heavy inputs: when x does not fit L2 and consecutive rows look at unrelated parts of it
+// (uniform-random columns), every gather is a DRAM sector of its own and the kernel is bound by gathers in
+// flight, not by the A stream: sub-warp-per-row VECTOR keeps more of them in flight than PIPE's staged tiles
+// (16M x 32 uniform-random, fp64: 5.6 ms against 7.4 ms).  One tiny kernel + one 16-byte copy, once per plan.
+template <typename T>
+static bool gather_heavy(cudaStream_t st, sblasPlan_st* plan, const int32_t* rp, const int32_t* ci, int32_t rows,
+                         int32_t cols) {
+  if ((size_t)cols * sizeof(T) <= kGatherHeavyXBytes || rows < 4096 || plan->nnz == 0) return false;
+  if (plan->col_jump < 0.0) {
+    void* scratch = nullptr;
+    if (plan_scratch(plan, 64, &scratch)) return false;
+    double h[2] = {0.0, 0.0};
+    if (cudaMemsetAsync(scratch, 0, 16, st) != cudaSuccess) return false;
+    col_jump_kernel<<<16, 256, 0, st>>>(rp, ci, rows, 4096, (double*)scratch);
+    ++g_launches;
+    if (cudaMemcpyAsync(h, scratch, 16, cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+        cudaStreamSynchronize(st) != cudaSuccess)
+      return false;
+    plan->col_jump = h[1] > 0.0 ? h[0] / h[1] : 0.0;
+  }
+  return plan->col_jump > (double)cols / 256.0;
+}
+
 template <typename T>
 static int resolve_variant(const sblasPlan_st* plan, const sblasOpts* o, int32_t tile) {
   if (o && o->variant != SBLAS_VARIANT_AUTO) return o->variant;
@@ -919,6 +971,12 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
     plan = eph;
   }
   if (plan) SBLAS_CHECK(plan->rows == rows && plan->nnz == nnz, "spmv: plan does not match matrix");
+  bool auto_gather = false;
+  if (plan && variant == SBLAS_SPMV_PIPE && !(o && o->variant != SBLAS_VARIANT_AUTO) &&
+      gather_heavy<T>(st, plan, rp, ci, rows, cols)) {
+    variant = SBLAS_SPMV_VECTOR;
+    auto_gather = true;
+  }
   const bool vec = aligned16(ci) && aligned16(v);
   int rc = 0;
   if (variant == SBLAS_SPMV_PIPE && !(o && o->tile > 0))  // every row must fit a tile's staging buffer
@@ -1078,6 +1136,7 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
   }
   if (rc == 0 && variant == SBLAS_SPMV_VECTOR) {
     int lanes = (o && o->lanes > 0) ? o->lanes : pow2_lanes(rows ? (double)nnz / rows : 0.0);
+    if (auto_gather && !(o && o->lanes > 0)) lanes = std::min(32, lanes * 2);  // ~2 nnz per lane: more gathers in flight
     rc = (flags & SBLAS_FLAG_FMA) ? launch_vector<T, kSpmvBlock, true>(st, lanes, rows, rp, ci, v, x, sink)
                                   : launch_vector<T, kSpmvBlock, false>(st, lanes, rows, rp, ci, v, x, sink);
   }
@@ -1108,6 +1167,12 @@ int sblas_spmv_csr_f32(void* stream, int32_t rows, int32_t cols, int64_t nnz, co
                        const int32_t* ci, const float* v, const float* x, float* y, float alpha,
                        float beta, sblasPlan_t plan, const sblasOpts* opts) {
   return spmv_impl<float>((cudaStream_t)stream, rows, cols, nnz, rp, ci, v, x, y, alpha, beta, plan, opts);
+}
+
+int sblas_plan_col_jump(sblasPlan_t p, double* out) {
+  SBLAS_CHECK(p && out, "plan_col_jump: null");
+  *out = p->col_jump;
+  return 0;
 }
 
 int sblas_plan_stats(sblasPlan_t p, sblasCsrStats* out) {

@@ -170,6 +170,12 @@ class Plan:
         check(lib().sblas_plan_stats(self.handle, C.byref(st)), "plan_stats")
         return {f: getattr(st, f) for f, _ in st._fields_}
 
+    def col_jump(self):
+        """mean first-column jump between consecutive rows (-1 = not measured yet), see sblas_plan_col_jump"""
+        out = C.c_double()
+        check(lib().sblas_plan_col_jump(self.handle, C.byref(out)), "plan_col_jump")
+        return out.value
+
     def __del__(self):
         try:
             if self.handle:

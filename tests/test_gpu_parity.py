@@ -516,3 +516,32 @@ def test_coo_sort_and_loader(sblas, dev, oracle, golden, dtype):
     torch.cuda.synchronize()
     assert np.array_equal(dr.cpu().numpy(), rs) and np.array_equal(dc.cpu().numpy(), cs)
     assert np.array_equal(dv.cpu().numpy(), vs.astype(dtype))
+
+
+@pytest.mark.gpu
+def test_spmv_auto_gather_heavy(sblas, dev, oracle):
+    """AUTO on an input whose x does not fit L2: uniform-random columns switch to the sub-warp-per-row kernel
+    (plan statistic col_jump > cols/256), banded columns stay on the staged kernel; both match the oracle."""
+    import torch
+    K = sblas.kernels
+    rows, cols, deg = 20000, 14_000_000, 8
+    rng = np.random.default_rng(12)
+    rp = (np.arange(rows + 1, dtype=np.int64) * deg).astype(np.int32)
+    x = rng.random(cols)
+    y0 = rng.random(rows)
+    for kind in ("random", "banded"):
+        if kind == "random":
+            ci = np.sort(rng.integers(0, cols, (rows, deg)), axis=1).astype(np.int32).reshape(-1)
+        else:
+            ci = (np.arange(rows)[:, None] * 3 + np.arange(deg)[None, :]).astype(np.int32).reshape(-1)
+        v = rng.standard_normal(rows * deg)
+        ref = oracle.spmv(rp, ci, v, x, y0.copy(), 1.5, -0.5)
+        drp, dci, dv, dx, dy = (_t(dev, a) for a in (rp, ci, v, x, y0))
+        plan = K.Plan(drp, len(ci))
+        assert plan.col_jump() == -1.0
+        K.spmv(drp, dci, dv, dx, dy, 1.5, -0.5, plan=plan, cols=cols)
+        torch.cuda.synchronize()
+        cj = plan.col_jump()
+        assert (cj > cols / 256.0) == (kind == "random"), (kind, cj)
+        bound = _row_bound(oracle, rp, ci, v, x, 1.5, -0.5, y0)
+        _check(dy.cpu().numpy(), ref, bound, np.float64)
