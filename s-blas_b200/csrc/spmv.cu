@@ -385,12 +385,13 @@ struct PipeSplitSink {
 };
 
 template <typename T>
-struct SplitArgs {  // only read by the SPLIT instantiation
+struct SplitArgs {  // all but `consec` only read by the SPLIT instantiation
   int32_t T_items, rows;
   int64_t nnz;
   T* carry_out;
   T* head_val;
   int32_t* head_row;
+  int32_t consec;  // 1: CTA c walks a run of CONSECUTIVE tiles (x lines of neighbouring tiles stay in its L1)
 };
 
 template <typename T, int BLOCK, int NSTAGE, int G, bool SPLIT>
@@ -412,12 +413,16 @@ spmv_pipe_kernel(const int32_t* __restrict__ tile_row, const int32_t* __restrict
     mbar_fence_init();
   }
   __syncthreads();
-  const int my_tiles = ((int)n_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+  const int q_tiles = (int)n_tiles / (int)gridDim.x, r_tiles = (int)n_tiles % (int)gridDim.x;
+  const int my_tiles = sp.consec ? q_tiles + ((int)blockIdx.x < r_tiles ? 1 : 0)
+                                 : ((int)n_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+  const int64_t tile_base = sp.consec ? (int64_t)blockIdx.x * q_tiles + min((int)blockIdx.x, r_tiles) : (int64_t)blockIdx.x;
+  const int64_t tile_step = sp.consec ? 1 : (int64_t)gridDim.x;
 
   // descriptor of my i-th tile: (r0, r1, n0, n1) = local rows [r0, r1), nnz window [n0, n1)
   auto load_desc = [&](int i) -> int4 {
     if (i >= my_tiles) return make_int4(0, 0, 0, 0);
-    const int64_t b = (int64_t)blockIdx.x + (int64_t)i * gridDim.x;
+    const int64_t b = tile_base + (int64_t)i * tile_step;
     if (SPLIT) {
       // tile_row = merge-path split table (split_search_kernel): rows ra..rb-1 END in this tile,
       // row rb (if < rows) is cut by its end; nnz window from the merge diagonal
@@ -483,7 +488,7 @@ spmv_pipe_kernel(const int32_t* __restrict__ tile_row, const int32_t* __restrict
     const int4 d = descs[s];
     const int32_t r0 = d.x, nrows = SPLIT ? (d.y & 0xffffff) : d.y - d.x, n0 = d.z, n1 = d.w;
     if (SPLIT) {
-      const int64_t b = (int64_t)blockIdx.x + (int64_t)i * gridDim.x;
+      const int64_t b = tile_base + (int64_t)i * tile_step;
       const bool has_cut = (d.y >> 24) != 0;
       const int32_t nfin = nrows - (has_cut ? 1 : 0);               // rows r0 .. r0+nfin-1 end here
       const bool head_open = nfin > 0 && st.rp[0] < n0;
@@ -1011,6 +1016,13 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
           cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, plan->device);
           const int grid = std::min<int>(tt->n_tiles, n_sm * per_sm);
           SplitArgs<T> sp{};
+          // tile order: CTA c takes tiles c, c+grid, ... (the resident CTAs sweep one contiguous window of A and
+          // share x through L2: best while x fits L2, c2 74 us against 86 us) or a run of consecutive tiles (the x
+          // lines of neighbouring tiles stay in the CTA's own L1: best when x is larger than L2 and rows are local,
+          // b32 1.376 -> 1.323 ms).  col_jump is only measured for x > 96 MB (gather_heavy); SBLAS_PIPE_CONSEC=0/1
+          // overrides for experiments.
+          static const int env_consec = [] { const char* e = getenv("SBLAS_PIPE_CONSEC"); return e ? atoi(e) : -1; }();
+          sp.consec = env_consec >= 0 ? env_consec : (plan->col_jump >= 0.0 && !auto_gather ? 1 : 0);
           void* args[] = {(void*)&tt->d_tile_row, (void*)&tt->d_tile_nnz, (void*)&tt->n_tiles, (void*)&rp,
                           (void*)&ci, (void*)&v, (void*)&x, (void*)&sink, (void*)&cap_nnz,
                           (void*)&cap_rows, (void*)&sp};
@@ -1089,7 +1101,7 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
           int n_sm = kNumSM;
           cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, plan->device);
           const int grid = std::min<int>(tt->n_tiles, n_sm * per_sm);
-          SplitArgs<T> sp{tile, rows, nnz, carry_out, head_val, head_row};
+          SplitArgs<T> sp{tile, rows, nnz, carry_out, head_val, head_row, 0};
           const int32_t* no_nnz_table = nullptr;
           void* args[] = {(void*)&tt->d_tile_row, (void*)&no_nnz_table, (void*)&tt->n_tiles, (void*)&rp,
                           (void*)&ci, (void*)&v, (void*)&x, (void*)&sink, (void*)&cap_nnz,
