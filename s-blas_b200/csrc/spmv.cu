@@ -1019,10 +1019,14 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
           // tile order: CTA c takes tiles c, c+grid, ... (the resident CTAs sweep one contiguous window of A and
           // share x through L2: best while x fits L2, c2 74 us against 86 us) or a run of consecutive tiles (the x
           // lines of neighbouring tiles stay in the CTA's own L1: best when x is larger than L2 and rows are local,
-          // b32 1.376 -> 1.323 ms).  col_jump is only measured for x > 96 MB (gather_heavy); SBLAS_PIPE_CONSEC=0/1
-          // overrides for experiments.
+          // b32 1.376 -> 1.323 ms).  The part of x these rows touch is estimated as rows * col_jump elements (local
+          // rows advance col_jump columns per row; a row panel of a larger matrix touches only its own window of x);
+          // col_jump is only measured when the whole x exceeds 96 MB (gather_heavy).  SBLAS_PIPE_CONSEC=0/1 overrides
+          // for experiments.
           static const int env_consec = [] { const char* e = getenv("SBLAS_PIPE_CONSEC"); return e ? atoi(e) : -1; }();
-          sp.consec = env_consec >= 0 ? env_consec : (plan->col_jump >= 0.0 && !auto_gather ? 1 : 0);
+          const bool big_window = plan->col_jump >= 0.0 && !auto_gather &&
+                                  plan->col_jump * (double)rows * sizeof(T) > (double)kGatherHeavyXBytes;
+          sp.consec = env_consec >= 0 ? env_consec : (big_window ? 1 : 0);
           void* args[] = {(void*)&tt->d_tile_row, (void*)&tt->d_tile_nnz, (void*)&tt->n_tiles, (void*)&rp,
                           (void*)&ci, (void*)&v, (void*)&x, (void*)&sink, (void*)&cap_nnz,
                           (void*)&cap_rows, (void*)&sp};
