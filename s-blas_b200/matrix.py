@@ -233,3 +233,82 @@ class DenseMatrix:
                 K.axpby(self.val_gpu[i], dm.val_gpu[i], alpha, beta)
         for i in range(self.n_gpu):
             torch.cuda.synchronize(physical(i))
+
+
+# ---- format containers beside CSR (matrix.h:40-272, :457-506) -----------------------
+def CsrToCsc(m, n, nnz, csrRowPtr, csrColIdx, csrVal):
+    """matrix.h:40-64 on host arrays (the work runs on GPU 0): -> (cscRowIdx, cscColPtr, cscVal),
+    inside a column the entries keep CSR order, bit-identical to the reference's CPU loop."""
+    torch = _torch()
+    with torch.cuda.device(physical(0)):
+        cp, ri, cv = K.csr2csc(int(m), int(n), _to_dev(np.asarray(csrRowPtr, np.int32), 0),
+                               _to_dev(np.asarray(csrColIdx, np.int32)[:nnz], 0), _to_dev(np.asarray(csrVal)[:nnz], 0))
+        torch.cuda.synchronize()
+    return ri.cpu().numpy(), cp.cpu().numpy(), cv.cpu().numpy()
+
+
+def CscToCsr(n, m, nnz, cscColPtr, cscRowIdx, cscVal):
+    """matrix.h:67-91 (the reference's argument order n, m): -> (csrColIdx, csrRowPtr, csrVal)."""
+    torch = _torch()
+    with torch.cuda.device(physical(0)):
+        rp, ci, cv = K.csc2csr(int(n), int(m), _to_dev(np.asarray(cscColPtr, np.int32), 0),
+                               _to_dev(np.asarray(cscRowIdx, np.int32)[:nnz], 0), _to_dev(np.asarray(cscVal)[:nnz], 0))
+        torch.cuda.synchronize()
+    return ci.cpu().numpy(), rp.cpu().numpy(), cv.cpu().numpy()
+
+
+class CooSparseMatrix:
+    """matrix.h:117-272: entries as the .mtx file holds them (no symmetric expansion, :165-173), sorted by
+    (row, col) on GPU 0 (sortByRow, :221-237; equal pairs keep file order), then replicated or cut into
+    floor(nnz / n_gpu)-sized pieces (:196-216)."""
+
+    def __init__(self, path=None, n_gpu=0, policy=none, dtype=np.float64):
+        self.cooRowIdx = self.cooColIdx = self.cooVal = None
+        self.cooRowIdx_gpu = self.cooColIdx_gpu = self.cooVal_gpu = self.nnz_gpu = None
+        self.nnz = self.height = self.width = 0
+        self.n_gpu, self.policy = 0, none
+        if path is None:
+            return
+        print("Loading input matrix from '%s'." % path)
+        self.height, self.width, r, c, v = K.read_mtx_coo(path)
+        self.nnz = len(r)
+        print("Height: %d Width: %d nnz: %d" % (self.height, self.width, self.nnz))
+        self.cooRowIdx, self.cooColIdx, self.cooVal = r, c, v.astype(_np_dtype(dtype))
+        self.sortByRow()
+        self.n_gpu, self.policy = n_gpu, policy
+        if n_gpu != 0 and policy != none:
+            avg = self.nnz // n_gpu                                   # matrix.h:198
+            self.nnz_gpu = np.array([(min((i + 1) * avg, self.nnz) - i * avg) if policy == segment else self.nnz
+                                     for i in range(n_gpu)], np.int32)
+            self.cooRowIdx_gpu, self.cooColIdx_gpu, self.cooVal_gpu = [], [], []
+            for i in range(n_gpu):
+                lo = i * avg if policy == segment else 0
+                hi = lo + int(self.nnz_gpu[i])
+                self.cooRowIdx_gpu.append(_to_dev(self.cooRowIdx[lo:hi], i))
+                self.cooColIdx_gpu.append(_to_dev(self.cooColIdx[lo:hi], i))
+                self.cooVal_gpu.append(_to_dev(self.cooVal[lo:hi], i))
+
+    def sortByRow(self):
+        if self.nnz == 0:
+            return
+        torch = _torch()
+        with torch.cuda.device(physical(0)):
+            r, c, v = (_to_dev(a, 0) for a in (self.cooRowIdx, self.cooColIdx, self.cooVal))
+            K.coo_sort(self.height, r, c, v)
+            torch.cuda.synchronize()
+        self.cooRowIdx, self.cooColIdx, self.cooVal = r.cpu().numpy(), c.cpu().numpy(), v.cpu().numpy()
+
+
+class CscSparseMatrix:
+    """matrix.h:457-506: built from a CsrSparseMatrix by CsrToCsc."""
+
+    def __init__(self, csr=None):
+        self.cscRowIdx = self.cscColPtr = self.cscVal = None
+        self.nnz = self.height = self.width = 0
+        if csr is None:
+            return
+        self.height, self.width, self.nnz = csr.height, csr.width, csr.nnz
+        print("Building csc matrix from a csr matrix.")
+        print("Height: %d Width: %d nnz: %d" % (self.height, self.width, self.nnz))
+        self.cscRowIdx, self.cscColPtr, self.cscVal = CsrToCsc(self.height, self.width, self.nnz, csr.csrRowPtr,
+                                                               csr.csrColIdx, csr.csrVal)

@@ -545,3 +545,20 @@ def test_spmv_auto_gather_heavy(sblas, dev, oracle):
         assert (cj > cols / 256.0) == (kind == "random"), (kind, cj)
         bound = _row_bound(oracle, rp, ci, v, x, 1.5, -0.5, y0)
         _check(dy.cpu().numpy(), ref, bound, np.float64)
+
+
+@pytest.mark.gpu
+def test_python_container_mirrors(sblas, oracle, golden):
+    """The host mirror's CooSparseMatrix / CscSparseMatrix / CsrToCsc / CscToCsr (unit_test.cu:20-51)."""
+    A = sblas.CsrSparseMatrix(golden["ash85_path"])
+    csc = sblas.CscSparseMatrix(A)
+    cp, ri, cv = oracle.csr2csc(A.height, A.width, A.csrRowPtr, A.csrColIdx, A.csrVal)
+    assert np.array_equal(csc.cscColPtr, cp) and np.array_equal(csc.cscRowIdx, ri) and np.array_equal(csc.cscVal, cv)
+    ci2, rp2, v2 = sblas.CscToCsr(A.width, A.height, A.nnz, csc.cscColPtr, csc.cscRowIdx, csc.cscVal)
+    assert np.array_equal(rp2, A.csrRowPtr) and all(
+        np.all(np.diff(ci2[rp2[r]:rp2[r + 1]]) >= 0) for r in range(A.height))
+    coo = sblas.CooSparseMatrix(golden["ash85_path"], 2, sblas.segment)
+    assert coo.nnz == 304 and list(coo.nnz_gpu) == [152, 152]
+    key = coo.cooRowIdx.astype(np.int64) * coo.width + coo.cooColIdx
+    assert np.all(np.diff(key) >= 0)
+    assert np.array_equal(coo.cooRowIdx_gpu[1].cpu().numpy(), coo.cooRowIdx[152:])
