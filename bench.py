@@ -721,7 +721,7 @@ def main():
     ap.add_argument("--scale-down", type=int, default=1, help="shrink the workload (smoke runs)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--e2e-steps", type=int, default=10)
+    ap.add_argument("--e2e-steps", type=int, default=100, help="steps of the end-to-end leg (pipeline fill and drain are inside its timed region)")
     ap.add_argument("--cpu-seconds", type=float, default=10.0)
     ap.add_argument("--ref-seconds", type=float, default=60.0)
     args = ap.parse_args()
