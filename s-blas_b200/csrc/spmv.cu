@@ -385,16 +385,16 @@ struct PipeSplitSink {
 };
 
 template <typename T>
-struct SplitArgs {  // all but `consec` only read by the SPLIT instantiation
+struct SplitArgs {  // only read by the SPLIT instantiation
   int32_t T_items, rows;
   int64_t nnz;
   T* carry_out;
   T* head_val;
   int32_t* head_row;
-  int32_t consec;  // 1: CTA c walks a run of CONSECUTIVE tiles (x lines of neighbouring tiles stay in its L1)
 };
 
-template <typename T, int BLOCK, int NSTAGE, int G, bool SPLIT>
+// CONSEC: CTA c walks a run of CONSECUTIVE tiles instead of c, c + grid, ... (see the host side)
+template <typename T, int BLOCK, int NSTAGE, int G, bool SPLIT, bool CONSEC = false>
 __global__ void __launch_bounds__(BLOCK)
 spmv_pipe_kernel(const int32_t* __restrict__ tile_row, const int32_t* __restrict__ tile_nnz,
                  int32_t n_tiles, const int32_t* __restrict__ rowptr,
@@ -413,16 +413,22 @@ spmv_pipe_kernel(const int32_t* __restrict__ tile_row, const int32_t* __restrict
     mbar_fence_init();
   }
   __syncthreads();
-  const int q_tiles = (int)n_tiles / (int)gridDim.x, r_tiles = (int)n_tiles % (int)gridDim.x;
-  const int my_tiles = sp.consec ? q_tiles + ((int)blockIdx.x < r_tiles ? 1 : 0)
-                                 : ((int)n_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
-  const int64_t tile_base = sp.consec ? (int64_t)blockIdx.x * q_tiles + min((int)blockIdx.x, r_tiles) : (int64_t)blockIdx.x;
-  const int64_t tile_step = sp.consec ? 1 : (int64_t)gridDim.x;
+  int my_tiles;
+  int64_t tile_base;
+  if (CONSEC) {
+    const int q_tiles = (int)n_tiles / (int)gridDim.x, r_tiles = (int)n_tiles % (int)gridDim.x;
+    my_tiles = q_tiles + ((int)blockIdx.x < r_tiles ? 1 : 0);
+    tile_base = (int64_t)blockIdx.x * q_tiles + min((int)blockIdx.x, r_tiles);
+  } else {
+    my_tiles = ((int)n_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+    tile_base = (int64_t)blockIdx.x;
+  }
+  auto tile_of = [&](int i) -> int64_t { return CONSEC ? tile_base + i : tile_base + (int64_t)i * gridDim.x; };
 
   // descriptor of my i-th tile: (r0, r1, n0, n1) = local rows [r0, r1), nnz window [n0, n1)
   auto load_desc = [&](int i) -> int4 {
     if (i >= my_tiles) return make_int4(0, 0, 0, 0);
-    const int64_t b = tile_base + (int64_t)i * tile_step;
+    const int64_t b = tile_of(i);
     if (SPLIT) {
       // tile_row = merge-path split table (split_search_kernel): rows ra..rb-1 END in this tile,
       // row rb (if < rows) is cut by its end; nnz window from the merge diagonal
@@ -488,7 +494,7 @@ spmv_pipe_kernel(const int32_t* __restrict__ tile_row, const int32_t* __restrict
     const int4 d = descs[s];
     const int32_t r0 = d.x, nrows = SPLIT ? (d.y & 0xffffff) : d.y - d.x, n0 = d.z, n1 = d.w;
     if (SPLIT) {
-      const int64_t b = tile_base + (int64_t)i * tile_step;
+      const int64_t b = tile_of(i);
       const bool has_cut = (d.y >> 24) != 0;
       const int32_t nfin = nrows - (has_cut ? 1 : 0);               // rows r0 .. r0+nfin-1 end here
       const bool head_open = nfin > 0 && st.rp[0] < n0;
@@ -870,9 +876,9 @@ static int pow2_lanes_pipe(double avg) {
   return avg <= 6 ? 1 : avg <= 12 ? 2 : avg <= 24 ? 4 : avg <= 48 ? 8 : avg <= 96 ? 16 : 32;
 }
 
-template <typename T, bool SPLIT>
+template <typename T, bool SPLIT, bool CONSEC = false>
 static const void* pipe_kernel_ptr(int stages, int G) {
-#define SBLAS_PK(NS, GG) (const void*)spmv_pipe_kernel<T, kSpmvBlock, NS, GG, SPLIT>
+#define SBLAS_PK(NS, GG) (const void*)spmv_pipe_kernel<T, kSpmvBlock, NS, GG, SPLIT, CONSEC>
 #define SBLAS_PKG(NS)                                                                          \
   (G <= 1 ? SBLAS_PK(NS, 1) : G == 2 ? SBLAS_PK(NS, 2) : G == 4 ? SBLAS_PK(NS, 4)               \
    : G == 8 ? SBLAS_PK(NS, 8) : G == 16 ? SBLAS_PK(NS, 16) : SBLAS_PK(NS, 32))
@@ -1005,7 +1011,18 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
         // lanes per row from the mean row length (one instantiation per launch keeps the
         // kernel small: ~50 registers instead of 160 with an in-kernel switch)
         int G = (o && o->lanes > 0) ? o->lanes : pow2_lanes_pipe(rows ? (double)(nnz / rows) : 0.0);  // integer mean, as the per-tile rule of TILE
-        const void* kern = pipe_kernel_ptr<T, false>(stages, G);
+        // tile order: CTA c takes tiles c, c+grid, ... (the resident CTAs sweep one contiguous window of A and
+        // share x through L2: best while x fits L2, c2 74 us against 86 us) or a run of consecutive tiles (the x
+        // lines of neighbouring tiles stay in the CTA's own L1: best when x is larger than L2 and rows are local,
+        // b32 1.376 -> 1.323 ms).  The part of x these rows touch is estimated as rows * col_jump elements (local
+        // rows advance col_jump columns per row; a row panel of a larger matrix touches only its own window of x);
+        // col_jump is only measured when the whole x exceeds 96 MB (gather_heavy).  SBLAS_PIPE_CONSEC=0/1 overrides
+        // for experiments.  A template parameter: the strided instantiation is the kernel it always was.
+        static const int env_consec = [] { const char* e = getenv("SBLAS_PIPE_CONSEC"); return e ? atoi(e) : -1; }();
+        const bool big_window = plan->col_jump >= 0.0 && !auto_gather &&
+                                plan->col_jump * (double)rows * sizeof(T) > (double)kGatherHeavyXBytes;
+        const bool consec = env_consec >= 0 ? env_consec != 0 : big_window;
+        const void* kern = consec ? pipe_kernel_ptr<T, false, true>(stages, G) : pipe_kernel_ptr<T, false>(stages, G);
         int per_sm = 0;
         if ((rc = set_smem_once<T>(kern, smem)) == 0) {
           cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kSpmvBlock, smem);
@@ -1016,17 +1033,6 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
           cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, plan->device);
           const int grid = std::min<int>(tt->n_tiles, n_sm * per_sm);
           SplitArgs<T> sp{};
-          // tile order: CTA c takes tiles c, c+grid, ... (the resident CTAs sweep one contiguous window of A and
-          // share x through L2: best while x fits L2, c2 74 us against 86 us) or a run of consecutive tiles (the x
-          // lines of neighbouring tiles stay in the CTA's own L1: best when x is larger than L2 and rows are local,
-          // b32 1.376 -> 1.323 ms).  The part of x these rows touch is estimated as rows * col_jump elements (local
-          // rows advance col_jump columns per row; a row panel of a larger matrix touches only its own window of x);
-          // col_jump is only measured when the whole x exceeds 96 MB (gather_heavy).  SBLAS_PIPE_CONSEC=0/1 overrides
-          // for experiments.
-          static const int env_consec = [] { const char* e = getenv("SBLAS_PIPE_CONSEC"); return e ? atoi(e) : -1; }();
-          const bool big_window = plan->col_jump >= 0.0 && !auto_gather &&
-                                  plan->col_jump * (double)rows * sizeof(T) > (double)kGatherHeavyXBytes;
-          sp.consec = env_consec >= 0 ? env_consec : (big_window ? 1 : 0);
           void* args[] = {(void*)&tt->d_tile_row, (void*)&tt->d_tile_nnz, (void*)&tt->n_tiles, (void*)&rp,
                           (void*)&ci, (void*)&v, (void*)&x, (void*)&sink, (void*)&cap_nnz,
                           (void*)&cap_rows, (void*)&sp};
@@ -1105,7 +1111,7 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
           int n_sm = kNumSM;
           cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, plan->device);
           const int grid = std::min<int>(tt->n_tiles, n_sm * per_sm);
-          SplitArgs<T> sp{tile, rows, nnz, carry_out, head_val, head_row, 0};
+          SplitArgs<T> sp{tile, rows, nnz, carry_out, head_val, head_row};
           const int32_t* no_nnz_table = nullptr;
           void* args[] = {(void*)&tt->d_tile_row, (void*)&no_nnz_table, (void*)&tt->n_tiles, (void*)&rp,
                           (void*)&ci, (void*)&v, (void*)&x, (void*)&sink, (void*)&cap_nnz,
