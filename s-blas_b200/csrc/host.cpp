@@ -10,7 +10,9 @@
 #include <thread>
 #include <vector>
 
+#include <fcntl.h>
 #include <sys/stat.h>
+#include <unistd.h>
 
 #include "sblas_b200.h"
 
@@ -128,10 +130,41 @@ int sblas_csr_partition_rows_i32(const int32_t* rowptr, int32_t height, unsigned
 // sblas_mtx_info keeps the parsed file until the matching sblas_mtx_data call, so the usual
 // info -> allocate -> data sequence (matrix.h:303-318) parses the file once, not twice.
 namespace {
+// Uninitialised array: std::vector would zero-fill (one extra pass and, worse, every page first touched by ONE
+// thread); here the parser threads are the first to touch their own slots.
+template <typename T>
+class RawArray {
+ public:
+  RawArray() = default;
+  RawArray(const RawArray&) = delete;
+  RawArray& operator=(const RawArray&) = delete;
+  RawArray(RawArray&& o) noexcept : p_(o.p_), n_(o.n_) { o.p_ = nullptr; o.n_ = 0; }
+  RawArray& operator=(RawArray&& o) noexcept {
+    if (this != &o) { free(p_); p_ = o.p_; n_ = o.n_; o.p_ = nullptr; o.n_ = 0; }
+    return *this;
+  }
+  ~RawArray() { free(p_); }
+  bool resize(size_t n) {
+    free(p_);
+    p_ = n ? (T*)malloc(n * sizeof(T)) : nullptr;
+    n_ = (n && !p_) ? 0 : n;
+    return n == 0 || p_ != nullptr;
+  }
+  size_t size() const { return n_; }
+  T* data() { return p_; }
+  const T* data() const { return p_; }
+  T& operator[](size_t i) { return p_[i]; }
+  const T& operator[](size_t i) const { return p_[i]; }
+
+ private:
+  T* p_ = nullptr;
+  size_t n_ = 0;
+};
+
 struct Mtx {
   int m = 0, n = 0, sym = 0;
-  std::vector<int32_t> ri, cj;
-  std::vector<double> v;
+  RawArray<int32_t> ri, cj;
+  RawArray<double> v;
 };
 
 int g_mtx_threads = 0;  // 0 = auto
@@ -194,14 +227,29 @@ static inline const char* parse_entry(const char* p, const char* e, Field fld, i
 }
 
 static int load_mtx(const char* fn, Mtx& M) {
-  FILE* f = fopen(fn, "rb");
-  if (!f) { set_error("mtx: cannot open %s", fn); return -1; }
-  fseek(f, 0, SEEK_END);
-  long sz = ftell(f);
-  fseek(f, 0, SEEK_SET);
-  std::string buf((size_t)std::max(sz, 0l) + 1, '\0');  // NUL behind the text: strtol/strtod stop there
-  if (sz > 0 && fread(&buf[0], 1, (size_t)sz, f) != (size_t)sz) { fclose(f); set_error("mtx: short read"); return -1; }
-  fclose(f);
+  const int fd = open(fn, O_RDONLY);
+  if (fd < 0) { set_error("mtx: cannot open %s", fn); return -1; }
+  struct stat fst;
+  if (fstat(fd, &fst) != 0 || !S_ISREG(fst.st_mode)) { close(fd); set_error("mtx: cannot stat %s", fn); return -1; }
+  const long sz = (long)fst.st_size;
+  RawArray<char> buf;  // not zero-filled; one NUL behind the text: strtol/strtod stop there
+  if (!buf.resize((size_t)std::max(sz, 0l) + 1)) { close(fd); set_error("mtx: out of memory reading %s", fn); return -1; }
+  {  // the file is read by the same threads that parse it (pread of disjoint slices)
+    const int TR = mtx_thread_count((size_t)std::max(sz, 0l));
+    std::vector<int> bad((size_t)TR, 0);
+    run_threads(TR, [&](int t) {
+      size_t lo = (size_t)sz * (size_t)t / (size_t)TR, hi = (size_t)sz * (size_t)(t + 1) / (size_t)TR;
+      while (lo < hi) {
+        const ssize_t got = pread(fd, buf.data() + lo, hi - lo, (off_t)lo);
+        if (got <= 0) { bad[(size_t)t] = 1; break; }
+        lo += (size_t)got;
+      }
+    });
+    close(fd);
+    for (int t = 0; t < TR; ++t)
+      if (bad[(size_t)t]) { set_error("mtx: short read"); return -1; }
+  }
+  buf[(size_t)std::max(sz, 0l)] = '\0';
   const char *p = buf.data(), *e = p + (size_t)std::max(sz, 0l);
   // banner: %%MatrixMarket matrix coordinate <type> <symmetry>
   char w[5][64] = {{0}};
@@ -232,7 +280,10 @@ static int load_mtx(const char* fn, Mtx& M) {
     nz = strtol(p, &q, 10); p = q;
     if (M.m < 0 || M.n < 0 || nz < 0) { set_error("mtx: bad size line"); return -4; }
   }
-  M.ri.resize((size_t)nz); M.cj.resize((size_t)nz); M.v.resize((size_t)nz);
+  if (!M.ri.resize((size_t)nz) || !M.cj.resize((size_t)nz) || !M.v.resize((size_t)nz)) {
+    set_error("mtx: out of memory for %ld entries", nz);
+    return -1;
+  }
   p = skip_ws(p, e);
   const size_t len = (size_t)(e - p);
   const int T = mtx_thread_count(len);
