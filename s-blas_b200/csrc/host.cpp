@@ -209,17 +209,93 @@ static void run_threads(int T, F&& fn) {
 
 enum Field { F_REAL, F_CPLX, F_INT, F_PAT };
 
+// Decimal index token -> long, exactly what strtol(p, &q, 10) returns for [+-]digits (the only form Matrix Market
+// indices take); anything else (or > 18 digits) goes to strtol itself.  *end = first unparsed character.
+static inline long fast_long(const char* p, const char** end) {
+  const char* s = p;
+  bool neg = false;
+  if (*s == '-' || *s == '+') { neg = *s == '-'; ++s; }
+  const char* d0 = s;
+  unsigned long v = 0;
+  while ((unsigned)(*s - '0') <= 9u) { v = v * 10u + (unsigned)(*s - '0'); ++s; }
+  if (s == d0 || s - d0 > 18) {
+    char* q = nullptr;
+    const long r = strtol(p, &q, 10);
+    *end = q > p ? q : p;
+    return r;
+  }
+  *end = s;
+  return neg ? -(long)v : (long)v;
+}
+
+// Decimal real token -> double.  Fast path (Clinger): a mantissa of at most 15 significant digits is exact in a
+// double, so is 10^|e| for |e| <= 22, and ONE correctly rounded multiply or divide gives the correctly rounded
+// result — bit-identical to strtod.  Everything else (longer mantissas such as %.17g output, large exponents,
+// inf / nan / hex floats, malformed tokens) is handed to strtod unchanged.
+static inline double fast_double(const char* p, const char** end) {
+  static const double kPow10[23] = {1e0,  1e1,  1e2,  1e3,  1e4,  1e5,  1e6,  1e7,  1e8,  1e9,  1e10, 1e11,
+                                    1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
+  const char* s = p;
+  bool neg = false;
+  if (*s == '-' || *s == '+') { neg = *s == '-'; ++s; }
+  unsigned long m = 0;
+  int digits = 0, frac = 0;
+  bool any = false;
+  while ((unsigned)(*s - '0') <= 9u) {
+    any = true;
+    if (m || *s != '0') { m = m * 10u + (unsigned)(*s - '0'); ++digits; }
+    ++s;
+    if (digits > 15) goto slow;
+  }
+  if (*s == '.') {
+    ++s;
+    while ((unsigned)(*s - '0') <= 9u) {
+      any = true;
+      if (m || *s != '0') { m = m * 10u + (unsigned)(*s - '0'); ++digits; }
+      ++frac;
+      ++s;
+      if (digits > 15 || frac > 300) goto slow;
+    }
+  }
+  if (!any) goto slow;
+  {
+    int e10 = 0;
+    if (*s == 'e' || *s == 'E') {
+      const char* t = s + 1;
+      bool eneg = false;
+      if (*t == '-' || *t == '+') { eneg = *t == '-'; ++t; }
+      if ((unsigned)(*t - '0') > 9u) goto slow;
+      int ev = 0;
+      while ((unsigned)(*t - '0') <= 9u) { ev = ev * 10 + (*t - '0'); ++t; if (ev > 1000) goto slow; }
+      e10 = eneg ? -ev : ev;
+      s = t;
+    }
+    if (!is_ws(*s) && *s != '\0') goto slow;  // trailing characters in the token (e.g. 'd' exponents): strtod decides
+    e10 -= frac;
+    if (e10 < -22 || e10 > 22) goto slow;
+    double v = (double)m;  // exact: m < 10^15 < 2^53
+    v = e10 < 0 ? v / kPow10[-e10] : v * kPow10[e10];
+    *end = s;
+    return neg ? -v : v;
+  }
+slow:
+  char* q = nullptr;
+  const double r = strtod(p, &q);
+  *end = q > p ? q : p;
+  return r;
+}
+
 // parse one entry whose first token starts at p; returns the position behind its last token
 static inline const char* parse_entry(const char* p, const char* e, Field fld, int32_t* r, int32_t* c, double* x) {
-  char* q = nullptr;
-  long a = strtol(p, &q, 10); p = skip_tok(q > p ? q : p, e); p = skip_ws(p, e);
-  long b = strtol(p, &q, 10); p = skip_tok(q > p ? q : p, e);
+  const char* q = p;
+  long a = fast_long(p, &q); p = skip_tok(q, e); p = skip_ws(p, e);
+  long b = fast_long(p, &q); p = skip_tok(q, e);
   double val = 1.0;
-  if (fld == F_REAL) { p = skip_ws(p, e); val = strtod(p, &q); p = skip_tok(q > p ? q : p, e); }
+  if (fld == F_REAL) { p = skip_ws(p, e); val = fast_double(p, &q); p = skip_tok(q, e); }
   else if (fld == F_CPLX) {
-    p = skip_ws(p, e); val = strtod(p, &q); p = skip_tok(q > p ? q : p, e);
+    p = skip_ws(p, e); val = fast_double(p, &q); p = skip_tok(q, e);
     p = skip_ws(p, e); p = skip_tok(p, e);  // imaginary part dropped (mmio_highlevel.h:192)
-  } else if (fld == F_INT) { p = skip_ws(p, e); val = (double)(int)strtol(p, &q, 10); p = skip_tok(q > p ? q : p, e); }
+  } else if (fld == F_INT) { p = skip_ws(p, e); val = (double)(int)fast_long(p, &q); p = skip_tok(q, e); }
   *r = (int32_t)(a - 1);
   *c = (int32_t)(b - 1);
   *x = val;

@@ -259,3 +259,29 @@ def test_choose_stitch(sblas):
     c4_panels = [38929, 223252, 327772, 594328, 983560, 1527264, 1056772, 3636731]   # R-MAT config 4, 8 GPUs
     rb = np.concatenate([[0], np.cumsum(c4_panels)])
     assert D.choose_stitch(rb, 8) == "mc"
+
+
+def test_mtx_loader_number_forms_bit_exact(sblas, oracle, tmp_path):
+    """The loader's fast decimal path (<= 15 significant digits, |exponent| <= 22: one exactly rounded multiply or
+    divide) and its strtod fallback return the same bits as the C library's parser, whatever the notation."""
+    rng = np.random.default_rng(21)
+    forms = ["%.3f", "%g", "%.10e", "%.15g", "%.16g", "%.17g", "%.1f", "%e", "%.12f", "%.15e"]
+    toks = []
+    for _ in range(4000):
+        v = float(rng.standard_normal() * 10.0 ** int(rng.integers(-30, 30)))
+        toks.append(forms[int(rng.integers(len(forms)))] % v)
+    toks += ["0", "-0.0", "+1.5", ".5", "5.", "1e22", "1e23", "1e-22", "1e-23", "123456789012345", "1234567890123456",
+             "999999999999999e22", "0.000001", "5e-324", "1.7976931348623157e308", "2.2250738585072014e-308",
+             "000123.4500", "1E5", "1e+5", "12345678901234567890", "0.1", "0.2", "0.3", "1e0", "100000000000000000000000"]
+    n = len(toks)
+    p = tmp_path / "forms.mtx"
+    with open(p, "w") as f:
+        f.write("%%%%MatrixMarket matrix coordinate real general\n%d %d %d\n" % (n, 3, n))
+        for i, t in enumerate(toks):
+            f.write("%d %d %s\n" % (i + 1, 1 + i % 3, t))
+    want = np.array([float(t) for t in toks])          # Python's float() is correctly rounded, like glibc strtod
+    for t in (1, 4):
+        h, w, rp, ci, v = sblas.kernels.read_mtx(str(p), threads=t)
+        assert np.array_equal(v.view(np.uint64), want.view(np.uint64)), np.nonzero(v != want)[0][:5]
+    ref = oracle.read_mtx(str(p))
+    assert np.array_equal(ref[4].view(np.uint64), want.view(np.uint64))
