@@ -371,6 +371,10 @@ class CsrSparseMatrix {
     /* SpMM row-block mirror of this GPU's rows (kept only for structured inputs, sblas_b200.h) */
     SBLAS_SAFE_CALL(sblas_plan_build_rowblocks_on((int)i, sizeof(DataType) == 8, plan_gpu[i],
                                                   (const int32_t*)csrColIdx_gpu[i], csrVal_gpu[i]));
+    /* SpMV: tile table + column-locality statistic now (no SpMV call then synchronises), and the column-panel
+       mirror of this GPU's rows when x will not stay in L2 (gather-heavy inputs only, sblas_b200.h) */
+    SBLAS_SAFE_CALL(sblas_plan_prepare_spmv_on((int)i, sizeof(DataType) == 8, plan_gpu[i],
+                                               (const int32_t*)csrColIdx_gpu[i], csrVal_gpu[i], (int32_t)width));
   }
   void release_gpu_() {
     if (plan_gpu != NULL) {

@@ -52,6 +52,9 @@ enum {
   SBLAS_SPMV_SPLIT = 3,   /* merge-path tiles that split long rows, carry fix-up (skewed inputs) */
   SBLAS_SPMV_PIPE = 4,    /* TILE's tiles walked by persistent CTAs; col_idx/val/rowptr/y of the next
                              tiles staged by TMA bulk copies + LDGSTS behind mbarriers (AUTO's choice) */
+  SBLAS_SPMV_COLPANEL = 5, /* one PIPE pass per column panel of the plan's column-panel mirror of A
+                              (sblas_plan_build_colpanels_*): each pass gathers from an L2-resident slice of x and
+                              carries the raw row sums to the next; AUTO's choice when the plan holds the mirror */
   SBLAS_SPMM_ROWMAJOR = 1, /* internal row-major B/C: one lane group per A row, 128-bit B gathers */
   SBLAS_SPMM_COLMAJOR = 2, /* native col-major B/C (the reference's host layout), no transposes */
   SBLAS_SPMM_ROWBLOCK = 3, /* row-major B/C on the plan's R x 1 row-block mirror of A: one B load feeds
@@ -65,9 +68,14 @@ enum {
                               shared memory).  On request only: measured level with ROWBLOCK_PIPE */
 };
 enum {
-  SBLAS_FLAG_FMA = 1,          /* allow fused multiply-add (default: separately rounded mul/add
-                                  in the sequential paths, bit-identical to spmv.h:22-31 /
-                                  spmm.h:56-68 on the CPU) */
+  SBLAS_FLAG_FMA = 1,          /* SpMV: allow fused multiply-add in the VECTOR variant (the other SpMV kernels
+                                  are HBM-bound and always use separately rounded mul/add, bit-identical to
+                                  spmv.h:22-31 for one lane per row).  SpMM: fused multiply-add (already the default) */
+  SBLAS_FLAG_EXACT = 1024,     /* SpMM: separately rounded multiply and add in CSR order, bit-identical to
+                                  sblas_spmm_csr_cpu (spmm.h:56-68), instead of the default fused multiply-add
+                                  (which stays within the north star's 1e-12 / 1e-5 relative row tolerance and
+                                  halves the FP64 instruction count).  SBLAS_EXACT=1 in the environment or
+                                  sblas_set_spmm_exact(1) make it the default; SBLAS_FLAG_FMA then opts out */
   SBLAS_FLAG_HEAD_PARTIAL = 2, /* local row 0 continues a row begun on the previous GPU
                                   (matrix.h:443-445): its sum goes to carry[0..k), not to y/C */
   SBLAS_FLAG_TAIL_PARTIAL = 4, /* local last row continues on the next GPU: sum -> carry[k..2k) */
@@ -179,6 +187,25 @@ SBLAS_API int sblas_plan_stats(sblasPlan_t plan, sblasCsrStats* out);
  * sample; -1 until an AUTO SpMV with an x larger than L2 measured it.  AUTO takes the sub-warp-per-row kernel
  * instead of the staged one when it exceeds cols / 256 (uniform-random columns: every gather its own sector). */
 SBLAS_API int sblas_plan_col_jump(sblasPlan_t plan, double* out);
+/* Takes at plan time what the first AUTO SpMV on the plan would otherwise do inside the call (and synchronise
+ * the stream for): the column-locality statistic when x (cols * elem_size bytes) is larger than ~L2, and the tile
+ * table of the staged kernel.  After it, sblas_spmv_csr_* on this plan never synchronises or allocates.
+ * CsrSparseMatrix::sync2gpu calls it (matrix.h:331-397 is where the reference does its per-GPU setup). */
+SBLAS_API int sblas_plan_prepare_i32(void* stream, sblasPlan_t plan, const int32_t* d_colidx, int32_t cols,
+                                     int32_t elem_size);
+/* Column-panel mirror of A for gather-heavy SpMV ("matrix.h device CSR layout", built inside
+ * CsrSparseMatrix::sync2gpu next to the CSR arrays of matrix.h:376-387): A split into n_panels column panels,
+ * each a CSR of its own that keeps the storage order of every row.  SpMV then runs one pass per panel, pass p
+ * gathering only from an L2-resident slice of x, the raw running row sums carried from pass to pass (rows whose
+ * columns ascend are still summed in CSR order).  n_panels = 0: automatic — built only when x (cols elements)
+ * exceeds 96 MB and the plan's col_jump statistic exceeds cols / 256 (uniform-random columns), with x slices
+ * of 32 MB (environment SBLAS_COLPANEL_MB); n_panels >= 1 forces that many panels (<= 32).  The mirror holds a
+ * COPY of col_idx / val: rebuild it after changing them. */
+SBLAS_API int sblas_plan_build_colpanels_f64(void* stream, sblasPlan_t plan, const int32_t* d_colidx,
+                                             const double* d_val, int32_t cols, int32_t n_panels);
+SBLAS_API int sblas_plan_build_colpanels_f32(void* stream, sblasPlan_t plan, const int32_t* d_colidx,
+                                             const float* d_val, int32_t cols, int32_t n_panels);
+SBLAS_API int sblas_plan_colpanel_stats(sblasPlan_t plan, int32_t* n_panels, int32_t* panel_cols);
 /* Row-block mirror of A for SpMM ("matrix.h device CSR layout", built inside
  * CsrSparseMatrix::sync2gpu next to the CSR arrays of matrix.h:376-387): R (= 4) consecutive rows
  * form a block row, every distinct column of a block row becomes one block {col, presence mask,
@@ -220,6 +247,12 @@ SBLAS_API int sblas_spmm_csr_f32(void* stream, int32_t rows, int32_t cols, int64
                                  const float* d_val, int32_t k, int32_t layout, const float* d_B,
                                  int64_t ldb, float* d_C, int64_t ldc, float alpha, float beta,
                                  sblasPlan_t plan, const sblasOpts* opts);
+
+/* Process-wide default arithmetic of sblas_spmm_csr_* calls that carry neither SBLAS_FLAG_EXACT nor
+ * SBLAS_FLAG_FMA: on != 0 -> separately rounded mul/add (bit-identical to spmm.h:56-68), 0 -> fused
+ * multiply-add (the initial default unless SBLAS_EXACT=1 is in the environment).  Returns the previous
+ * setting.  For callers that reach the kernels through the C++ headers and cannot pass flags. */
+SBLAS_API int sblas_set_spmm_exact(int on);
 
 /* kernel.h:28-37 denseVector_plusEqual_denseVector: v0[i] = v0[i]*beta + v1[i]*alpha. */
 SBLAS_API int sblas_axpby_f64(void* stream, double* d_v0, const double* d_v1, double alpha,
@@ -269,6 +302,9 @@ SBLAS_API int sblas_axpby_on(int gpu, int is_f64, void* d_v0, const void* d_v1, 
                              double beta, int64_t n);
 SBLAS_API int sblas_plan_build_rowblocks_on(int gpu, int is_f64, sblasPlan_t plan, const int32_t* d_colidx,
                                             const void* d_val);
+/* sblas_plan_prepare_i32 + sblas_plan_build_colpanels_* (automatic) on a logical GPU's default stream */
+SBLAS_API int sblas_plan_prepare_spmv_on(int gpu, int is_f64, sblasPlan_t plan, const int32_t* d_colidx,
+                                         const void* d_val, int32_t cols);
 SBLAS_API int sblas_scal_add_on(int gpu, int is_f64, void* d_v, double val, double beta, int64_t n);
 /* CsrToCsc / CscToCsr (matrix.h:40-91) and CooSparseMatrix::sortByRow (matrix.h:221-237) on a logical
  * GPU's default stream.  (m, n, d_ptr, d_idx) = (rows, cols, rowptr, colidx) for CSR -> CSC and
@@ -396,8 +432,11 @@ SBLAS_API int sblas_ipc_free(void* d_ptr);
  * SpMV/SpMM kernel in stream order, the wait returning means every peer's rows are in the local
  * replica: this completes the peer-store stitch with no host synchronisation and no collective
  * (the reference needs ncclAllReduce + two OpenMP barriers here, spmv.h:108-120).  Epochs must
- * increase by 1 per call on every rank.  A wait longer than ~2 s writes 1+peer into *d_status
- * (may be NULL) and returns instead of hanging.  At most 15 ranks. */
+ * increase by 1 per call on every rank.  A wait longer than SBLAS_BARRIER_TIMEOUT_MS (environment,
+ * default 20000, 0 = no limit) writes 1+peer into *d_status (may be NULL; sticky — the caller must read
+ * it before trusting the replica: a timed-out barrier leaves it INCOMPLETE) and returns instead of
+ * hanging; with SBLAS_BARRIER_TRAP=1 it also traps, so the stream itself reports the failure.
+ * At most 15 ranks. */
 SBLAS_API int sblas_peer_barrier(void* stream, int rank, int world, int32_t* d_local_flags,
                                  void* const* d_peer_flags, int32_t epoch, int32_t* d_status);
 

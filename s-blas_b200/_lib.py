@@ -10,7 +10,7 @@ LIB_PATH = os.path.join(HERE, "lib", "libsblas_b200.so")
 
 MAX_GPU = 16
 # enums of include/sblas_b200.h
-VARIANT_AUTO, SPMV_TILE, SPMV_VECTOR, SPMV_SPLIT, SPMV_PIPE = 0, 1, 2, 3, 4
+VARIANT_AUTO, SPMV_TILE, SPMV_VECTOR, SPMV_SPLIT, SPMV_PIPE, SPMV_COLPANEL = 0, 1, 2, 3, 4, 5
 SPMM_ROWMAJOR, SPMM_COLMAJOR, SPMM_ROWBLOCK, SPMM_ROWBLOCK_PIPE, SPMM_ROWBLOCK_TILEB = 1, 2, 3, 4, 5
 FLAG_FMA, FLAG_HEAD_PARTIAL, FLAG_TAIL_PARTIAL, FLAG_NO_L1 = 1, 2, 4, 8
 FLAG_PREFETCH_B, FLAG_NO_PREFETCH_B = 16, 32
@@ -18,6 +18,7 @@ FLAG_SPLIT_MERGE = 64
 FLAG_SPLIT_SERIAL = 128
 FLAG_SPLIT_SEG = 256
 FLAG_PREFETCH_C = 512
+FLAG_EXACT = 1024
 ROW_MAJOR, COL_MAJOR = 0, 1
 
 

@@ -19,7 +19,7 @@ OBJ = os.path.join(HERE, "_build")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libsblas_b200.so")
 
-SOURCES = ["plan.cu", "spmv.cu", "spmm.cu", "spmm_rb.cu", "dense.cu", "synth.cu", "mgpu.cu", "memory.cu", "convert.cu", "host.cpp"]
+SOURCES = ["plan.cu", "spmv.cu", "spmm.cu", "spmm_rb.cu", "colpanel.cu", "dense.cu", "synth.cu", "mgpu.cu", "memory.cu", "convert.cu", "host.cpp"]
 NVCC = os.environ.get("NVCC") or shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
          "-Wno-deprecated-gpu-targets", "-Wno-deprecated-declarations",

@@ -1,0 +1,176 @@
+// colpanel.cu — column-panel device mirror of A for gather-heavy SpMV (x larger than L2).
+//
+// Why: the north star's SpMV shape (16M rows x 32 nnz/row, uniform-random columns, fp64) has an x of
+// 134 MB against a 126 MB L2, and consecutive rows look at unrelated parts of it: every x gather is a
+// 32-byte DRAM sector of its own (536.9 M x 32 B = 17 GB of sector traffic beside 6.9 GB of compulsory
+// bytes), the kernel is bound by DRAM gathers in flight and sits at 19 % of the HBM roofline.  The lever
+// is the cache, and it is a data-layout question ("matrix.h: device CSR layout and padding" is one of
+// the subsystems the north star lets change): next to the CSR arrays the reference's API exposes,
+// sync2gpu builds a mirror of A split into P COLUMN PANELS, panel p = the nonzeros whose column lies in
+// [p*W, (p+1)*W), each panel a CSR of its own (row pointers [rows+1], col_idx / val in the original
+// order within a row).  y = beta*y + alpha*A*x then runs as P back-to-back passes of the PIPE kernel, pass p
+// touching only x[p*W, (p+1)*W) — a slice sized to stay L2-resident (default 32 MB: half of one L2
+// partition) while its panel of A streams by — and carrying the RAW running row sums in a scratch
+// vector: pass 0 writes sum_0, pass p continues the accumulation FROM the carried value (so a row
+// summed by one lane still adds its products in CSR storage order, one rounded multiply and one
+// rounded add each: bit-identical to spmv.h:24-30 when the row's columns ascend), the last pass
+// applies alpha and beta.  Extra traffic: P x (row pointers + carried sums read and written) =
+// P x 20 B per row, i.e. +19 % on the compulsory bytes at P = 4.
+//
+// Only built when it pays (sblas_plan_build_colpanels_*, n_panels = 0): x larger than 96 MB and the
+// plan's column-locality statistic says consecutive rows are far apart (col_jump > cols / 256).
+#include <cub/cub.cuh>
+
+#include "plan.cuh"
+
+namespace sblas {
+
+constexpr int kCpMaxPanels = 32;
+
+struct CpOffsets { int64_t off[kCpMaxPanels]; };
+
+// cnt[p*(rows+1) + r] = number of nonzeros of row r in panel p (entry [rows] of every panel = 0)
+__global__ void __launch_bounds__(256)
+cp_count_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colidx, int32_t rows,
+                int32_t W, int32_t P, int32_t* __restrict__ cnt) {
+  const int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (r > rows) return;
+  int32_t c[kCpMaxPanels];
+#pragma unroll
+  for (int p = 0; p < kCpMaxPanels; ++p) c[p] = 0;
+  if (r < rows) {
+    const int32_t s = rowptr[r], e = rowptr[r + 1];
+    for (int32_t j = s; j < e; ++j) c[min(colidx[j] / W, P - 1)]++;
+  }
+  for (int p = 0; p < P; ++p) cnt[(int64_t)p * (rows + 1) + r] = c[p];
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+cp_fill_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colidx, const T* __restrict__ val,
+               int32_t rows, int32_t W, int32_t P, const int32_t* __restrict__ prp, CpOffsets offs,
+               int32_t* __restrict__ oc, T* __restrict__ ov) {
+  const int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (r >= rows) return;
+  int64_t pos[kCpMaxPanels];
+  for (int p = 0; p < P; ++p) pos[p] = offs.off[p] + prp[(int64_t)p * (rows + 1) + r];
+  const int32_t s = rowptr[r], e = rowptr[r + 1];
+  for (int32_t j = s; j < e; ++j) {  // storage order of the row is kept inside every panel
+    const int32_t c = colidx[j];
+    const int64_t d = pos[min(c / W, P - 1)]++;
+    oc[d] = c;
+    ov[d] = val[j];
+  }
+}
+
+void colpanels_free(sblasPlan_st* plan) {
+  ColPanels& cp = plan->cp;
+  for (sblasPlan_st* s : cp.sub)
+    if (s) sblas_plan_destroy(s);
+  if (cp.d_rowptr) cudaFree(cp.d_rowptr);
+  if (cp.d_colidx) cudaFree(cp.d_colidx);
+  if (cp.d_val) cudaFree(cp.d_val);
+  if (cp.d_part) cudaFree(cp.d_part);
+  cp = ColPanels();
+}
+
+template <typename T>
+static int build_colpanels(cudaStream_t st, sblasPlan_st* plan, const int32_t* ci, const T* val, int32_t cols,
+                           int32_t n_panels) {
+  SBLAS_CHECK(plan && ci && val && cols > 0, "plan_build_colpanels: bad arguments");
+  colpanels_free(plan);
+  const int32_t rows = plan->rows;
+  if (rows == 0 || plan->nnz == 0) return 0;
+  int P = n_panels;
+  if (P == 0) {
+    // automatic: only for gather-heavy inputs, x slices of SBLAS_COLPANEL_MB (default 32) MB
+    if (!measure_gather_heavy(st, plan, plan->d_rowptr, ci, rows, cols, sizeof(T))) return 0;
+    static const int mb = [] { const char* e = getenv("SBLAS_COLPANEL_MB"); const int v = e ? atoi(e) : 0; return v > 0 ? v : 32; }();
+    P = (int)ceil_div((int64_t)cols * (int64_t)sizeof(T), (int64_t)mb << 20);
+    if (P < 2) return 0;
+  }
+  SBLAS_CHECK(P >= 1 && P <= kCpMaxPanels, "plan_build_colpanels: 1..%d panels", kCpMaxPanels);
+  const int32_t W = (int32_t)((ceil_div(cols, P) + 31) & ~(int64_t)31);
+  ColPanels& cp = plan->cp;
+  auto fail = [&](int rc) { colpanels_free(plan); return rc; };
+  const size_t rp_elems = (size_t)P * ((size_t)rows + 1);
+  if (cudaMalloc(&cp.d_rowptr, rp_elems * sizeof(int32_t)) != cudaSuccess) { set_error("plan_build_colpanels: out of device memory"); cudaGetLastError(); return fail(1); }
+  const int blocks = (int)ceil_div((int64_t)rows + 1, 256);
+  cp_count_kernel<<<blocks, 256, 0, st>>>(plan->d_rowptr, ci, rows, W, P, cp.d_rowptr);
+  ++g_launches;
+  // per panel: exclusive scan of the counts in place -> local row pointers; entry [rows] = panel nnz
+  size_t tb = 0;
+  void* tmp = nullptr;
+  if (cub::DeviceScan::ExclusiveSum(nullptr, tb, cp.d_rowptr, cp.d_rowptr, rows + 1, st) != cudaSuccess ||
+      cudaMalloc(&tmp, tb ? tb : 16) != cudaSuccess) { set_error("plan_build_colpanels: scan setup failed"); cudaGetLastError(); return fail(1); }
+  for (int p = 0; p < P; ++p) {
+    int32_t* c = cp.d_rowptr + (size_t)p * ((size_t)rows + 1);
+    if (cub::DeviceScan::ExclusiveSum(tmp, tb, c, c, rows + 1, st) != cudaSuccess) { cudaFree(tmp); set_error("plan_build_colpanels: scan failed"); cudaGetLastError(); return fail(1); }
+  }
+  std::vector<int32_t> tot((size_t)P, 0);
+  cudaError_t e = cudaSuccess;
+  for (int p = 0; p < P && e == cudaSuccess; ++p)
+    e = cudaMemcpyAsync(&tot[(size_t)p], cp.d_rowptr + (size_t)p * ((size_t)rows + 1) + rows, sizeof(int32_t), cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  cudaFree(tmp);
+  if (e != cudaSuccess) { set_error("plan_build_colpanels: %s", cudaGetErrorString(e)); cudaGetLastError(); return fail(1); }
+  CpOffsets offs;
+  cp.nnz_off.assign((size_t)P + 1, 0);
+  int64_t total = 0;
+  for (int p = 0; p < P; ++p) {
+    cp.nnz_off[(size_t)p] = total;
+    offs.off[p] = total;
+    total += ((int64_t)tot[(size_t)p] + 3) & ~(int64_t)3;  // every panel starts 16-byte aligned (TMA bulk staging)
+  }
+  cp.nnz_off[(size_t)P] = total;
+  for (int p = P; p < kCpMaxPanels; ++p) offs.off[p] = 0;
+  if (cudaMalloc(&cp.d_colidx, (size_t)std::max<int64_t>(total, 4) * sizeof(int32_t)) != cudaSuccess ||
+      cudaMalloc(&cp.d_val, (size_t)std::max<int64_t>(total, 4) * sizeof(T)) != cudaSuccess ||
+      cudaMalloc(&cp.d_part, (size_t)rows * sizeof(T)) != cudaSuccess) {
+    set_error("plan_build_colpanels: out of device memory for the mirror (%lld nnz)", (long long)total);
+    cudaGetLastError();
+    return fail(1);
+  }
+  cp_fill_kernel<T><<<(int)ceil_div(rows, 256), 256, 0, st>>>(plan->d_rowptr, ci, val, rows, W, P, cp.d_rowptr, offs,
+                                                            cp.d_colidx, (T*)cp.d_val);
+  ++g_launches;
+  if ((e = cudaGetLastError()) != cudaSuccess) { set_error("plan_build_colpanels: fill launch: %s", cudaGetErrorString(e)); return fail(3); }
+  // sub-plans: row statistics + the PIPE tile table of every panel, so that no SpMV call ever builds (and
+  // synchronises for) them
+  cp.n = P;
+  cp.panel_cols = W;
+  cp.is_f64 = sizeof(T) == 8;
+  cp.sub.assign((size_t)P, nullptr);
+  for (int p = 0; p < P; ++p) {
+    sblasPlan_st* sub = nullptr;
+    if (sblas_plan_create_i32(st, rows, tot[(size_t)p], cp.d_rowptr + (size_t)p * ((size_t)rows + 1), &sub)) return fail(4);
+    cp.sub[(size_t)p] = sub;
+    bool pipe_ok = false;
+    if (prepare_pipe_table(st, sub, &pipe_ok)) return fail(4);
+    if (!pipe_ok) {  // a panel row too long for the staging buffers: no mirror, the plain kernels take the input
+      colpanels_free(plan);
+      return 0;
+    }
+  }
+  return 0;
+}
+
+}  // namespace sblas
+
+using namespace sblas;
+extern "C" {
+int sblas_plan_build_colpanels_f64(void* stream, sblasPlan_t plan, const int32_t* d_colidx, const double* d_val,
+                                   int32_t cols, int32_t n_panels) {
+  return build_colpanels<double>((cudaStream_t)stream, plan, d_colidx, d_val, cols, n_panels);
+}
+int sblas_plan_build_colpanels_f32(void* stream, sblasPlan_t plan, const int32_t* d_colidx, const float* d_val,
+                                   int32_t cols, int32_t n_panels) {
+  return build_colpanels<float>((cudaStream_t)stream, plan, d_colidx, d_val, cols, n_panels);
+}
+int sblas_plan_colpanel_stats(sblasPlan_t plan, int32_t* n_panels, int32_t* panel_cols) {
+  SBLAS_CHECK(plan, "plan_colpanel_stats: null plan");
+  if (n_panels) *n_panels = plan->cp.n;
+  if (panel_cols) *panel_cols = plan->cp.panel_cols;
+  return 0;
+}
+}  // extern "C"

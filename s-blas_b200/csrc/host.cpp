@@ -347,13 +347,39 @@ static int load_mtx(const char* fn, Mtx& M) {
   const Field fld = is_real ? F_REAL : is_cplx ? F_CPLX : is_int ? F_INT : F_PAT;
   const int tpe = is_pat ? 2 : is_cplx ? 4 : 3;  // tokens per entry
   M.sym = (!strcmp(w[4], "symmetric") || !strcmp(w[4], "hermitian")) ? 1 : 0;
-  while (p < e && *p == '%') p = next_line(p, e);  // comments
+  // size line, read the way mm_read_mtx_crd_size does (mmio.h:338-366): lines with '%' in column 0 are
+  // comments; the first other line is tried as "M N nz" and consumed WHOLE (a fourth token on it is
+  // dropped with the line, as fgets + sscanf drop it); if it is not three integers (a blank line, an
+  // indented comment) it is discarded and the three integers are taken from the token stream behind it
+  // (the reference's fscanf loop), the entries starting right behind the third one.
+  while (p < e && *p == '%') p = next_line(p, e);
+  if (p >= e) { set_error("mtx: premature end of file before the size line"); return -4; }
   long nz = 0;
   {
-    char* q = nullptr;
-    M.m = (int)strtol(p, &q, 10); p = q;
-    M.n = (int)strtol(p, &q, 10); p = q;
-    nz = strtol(p, &q, 10); p = q;
+    const char* le = next_line(p, e);
+    auto three = [&](const char* s, const char* lim, const char** after) -> bool {
+      long vals[3];
+      for (int i = 0; i < 3; ++i) {
+        s = skip_ws(s, lim);
+        if (s >= lim) return false;
+        char* q = nullptr;
+        vals[i] = strtol(s, &q, 10);
+        if (q == s || q > lim) return false;
+        s = q;
+      }
+      M.m = (int)vals[0]; M.n = (int)vals[1]; nz = vals[2];
+      *after = s;
+      return true;
+    };
+    const char* after = nullptr;
+    if (three(p, le, &after)) {
+      p = le;
+    } else if (three(le, e, &after)) {
+      p = after;
+    } else {
+      set_error("mtx: malformed size line");
+      return -4;
+    }
     if (M.m < 0 || M.n < 0 || nz < 0) { set_error("mtx: bad size line"); return -4; }
   }
   if (!M.ri.resize((size_t)nz) || !M.cj.resize((size_t)nz) || !M.v.resize((size_t)nz)) {

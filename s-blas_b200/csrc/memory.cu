@@ -199,6 +199,14 @@ int sblas_plan_build_rowblocks_on(int gpu, int is_f64, sblasPlan_t plan, const i
   return is_f64 ? sblas_plan_build_rowblocks_f64(nullptr, plan, d_colidx, (const double*)d_val, 0)
                 : sblas_plan_build_rowblocks_f32(nullptr, plan, d_colidx, (const float*)d_val, 0);
 }
+int sblas_plan_prepare_spmv_on(int gpu, int is_f64, sblasPlan_t plan, const int32_t* d_colidx, const void* d_val, int32_t cols) {
+  if (!plan) return 0;
+  SBLAS_ON_GPU(gpu);
+  int rc = sblas_plan_prepare_i32(nullptr, plan, d_colidx, cols, is_f64 ? 8 : 4);
+  if (rc) return rc;
+  return is_f64 ? sblas_plan_build_colpanels_f64(nullptr, plan, d_colidx, (const double*)d_val, cols, 0)
+                : sblas_plan_build_colpanels_f32(nullptr, plan, d_colidx, (const float*)d_val, cols, 0);
+}
 // CsrToCsc / CscToCsr / sortByRow (matrix.h:40-91, :221-237) on a logical GPU's default stream; for
 // transpose_on, (m, n, ptr, idx) are (rows, cols, rowptr, colidx) for CSR -> CSC and (cols, rows,
 // colptr, rowidx) for CSC -> CSR.

@@ -71,24 +71,43 @@ static int launch_finish(cudaStream_t st, const FinishList& fl, const T* carry, 
 // system scope) until slot t of its own array reaches `epoch`.  The stores a rank's SpMV/SpMM
 // kernel made into the peers' replicas precede its flag store in stream order, so when the wait
 // returns every peer's rows have landed in the local replica.  Each rank owns one GPU, so the
-// spinning kernels of different ranks always run concurrently; the spin is bounded (about 2 s)
-// and reports a timeout through *status instead of hanging the device.
+// spinning kernels of different ranks always run concurrently; the spin is bounded (20 s of
+// %globaltimer by default, SBLAS_BARRIER_TIMEOUT_MS) and reports a timeout through the sticky
+// *status word — which RowSplitOp.check() turns into an exception — instead of hanging the device.
 __global__ void peer_barrier_kernel(int rank, int world, int32_t* local_flags, OutSpec<int32_t> peers,
-                                    int32_t epoch, int32_t* status) {
+                                    int32_t epoch, int32_t* status, unsigned long long timeout_ns, int trap) {
   const int t = threadIdx.x;
   if (t >= world) return;
   if (t != rank) {
     int32_t* dst = peers.ptr[t] + rank;
     asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(dst), "r"(epoch) : "memory");
-    const long long t0 = clock64();
+    unsigned long long t0, now;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
     int32_t v;
-    do {
+    for (;;) {
       asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(local_flags + t) : "memory");
       if (v - epoch >= 0) break;
       __nanosleep(64);
-    } while (clock64() - t0 < 4000000000ll);
-    if (v - epoch < 0 && status) atomicExch(status, 1 + t);
+      if (timeout_ns) {
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+        if (now - t0 > timeout_ns) break;
+      }
+    }
+    if (v - epoch < 0) {   // the replica is INCOMPLETE: say so (sticky), and fail the stream when asked to
+      if (status) atomicExch(status, 1 + t);
+      if (trap) __trap();
+    }
   }
+}
+
+// wait budget of the barrier: SBLAS_BARRIER_TIMEOUT_MS (default 20 000; 0 = wait for ever, e.g. under a
+// profiler that serialises the ranks), SBLAS_BARRIER_TRAP=1 turns a timeout into a device trap (the stream
+// then reports an error on its next synchronisation instead of only setting the status word)
+static void barrier_policy(unsigned long long* timeout_ns, int* trap) {
+  static const long long ms = [] { const char* e = getenv("SBLAS_BARRIER_TIMEOUT_MS"); return e ? atoll(e) : 20000ll; }();
+  static const int tr = [] { const char* e = getenv("SBLAS_BARRIER_TRAP"); return e ? atoi(e) : 0; }();
+  *timeout_ns = ms > 0 ? (unsigned long long)ms * 1000000ull : 0ull;
+  *trap = tr;
 }
 
 // ---- logical GPU -> physical device ------------------------------------------------------------
@@ -345,7 +364,10 @@ int sblas_peer_barrier(void* stream, int rank, int world, int32_t* d_local_flags
   for (int i = 0; i < SBLAS_MAX_GPU - 1; ++i) peers.ptr[i] = nullptr;
   SBLAS_CHECK(world <= SBLAS_MAX_GPU - 1, "peer_barrier: at most %d ranks", SBLAS_MAX_GPU - 1);
   for (int i = 0; i < world; ++i) peers.ptr[i] = (int32_t*)d_peer_flags[i];
-  peer_barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(rank, world, d_local_flags, peers, epoch, d_status);
+  unsigned long long timeout_ns = 0;
+  int trap = 0;
+  barrier_policy(&timeout_ns, &trap);
+  peer_barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(rank, world, d_local_flags, peers, epoch, d_status, timeout_ns, trap);
   SBLAS_LAUNCH_CHECK();
   return 0;
 }

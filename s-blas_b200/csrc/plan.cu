@@ -1,6 +1,8 @@
 // plan.cu — CSR row statistics + merge-path tile tables (see plan.cuh).
 #include <stdarg.h>
 
+#include <mutex>
+
 #include "plan.cuh"
 
 namespace sblas {
@@ -74,6 +76,44 @@ __global__ void tile_stats_kernel(const int32_t* __restrict__ rowptr,
   }
 }
 
+namespace {
+struct KernInfo { const void* kern; int device, block; size_t smem; int per_sm, n_sm; };
+struct KernAttr { const void* kern; int device; size_t max_smem; };
+std::mutex g_kern_mu;
+std::vector<KernInfo> g_kern_info;
+std::vector<KernAttr> g_kern_attr;
+}  // namespace
+
+int kernel_residency(const void* kern, int block, size_t smem, int* per_sm, int* n_sm) {
+  int device = 0;
+  SBLAS_CUDA(cudaGetDevice(&device));
+  std::lock_guard<std::mutex> lock(g_kern_mu);
+  for (const KernInfo& k : g_kern_info)
+    if (k.kern == kern && k.device == device && k.block == block && k.smem == smem) {
+      *per_sm = k.per_sm;
+      *n_sm = k.n_sm;
+      return 0;
+    }
+  if (smem > 48 * 1024) {  // opt-in limit: per function and device, only ever raised
+    SBLAS_CHECK(smem <= 227 * 1024, "kernel needs %zu bytes of shared memory", smem);
+    KernAttr* a = nullptr;
+    for (KernAttr& x : g_kern_attr)
+      if (x.kern == kern && x.device == device) a = &x;
+    if (!a || a->max_smem < smem) {
+      SBLAS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      if (a) a->max_smem = smem; else g_kern_attr.push_back({kern, device, smem});
+    }
+  }
+  KernInfo k{kern, device, block, smem, 0, kNumSM};
+  SBLAS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&k.per_sm, kern, block, smem));
+  SBLAS_CHECK(k.per_sm >= 1, "kernel does not fit an SM with %zu bytes of shared memory", smem);
+  SBLAS_CUDA(cudaDeviceGetAttribute(&k.n_sm, cudaDevAttrMultiProcessorCount, device));
+  g_kern_info.push_back(k);
+  *per_sm = k.per_sm;
+  *n_sm = k.n_sm;
+  return 0;
+}
+
 int plan_get_table(sblasPlan_st* plan, cudaStream_t stream, int32_t rw, int32_t T,
                    const TileTable** out) {
   for (const TileTable& t : plan->tables)
@@ -90,20 +130,29 @@ int plan_get_table(sblasPlan_st* plan, cudaStream_t stream, int32_t rw, int32_t 
   SBLAS_CHECK(nt < (1ll << 31) - 2, "plan: too many tiles");
   t.n_tiles = (int32_t)nt;
   int32_t* d_stats = nullptr;
-  SBLAS_CUDA(cudaMalloc(&t.d_tile_row, sizeof(int32_t) * (size_t)(t.n_tiles + 1)));
-  SBLAS_CUDA(cudaMalloc(&t.d_tile_nnz, sizeof(int32_t) * (size_t)(t.n_tiles + 1)));
-  SBLAS_CUDA(cudaMalloc(&d_stats, 2 * sizeof(int32_t)));
-  SBLAS_CUDA(cudaMemsetAsync(d_stats, 0, 2 * sizeof(int32_t), stream));
-  int blocks = (int)ceil_div(t.n_tiles + 1, 256);
-  tile_search_kernel<<<blocks, 256, 0, stream>>>(plan->d_rowptr, plan->rows, rw, T, t.n_tiles,
-                                                 t.d_tile_row, t.d_tile_nnz);
-  SBLAS_LAUNCH_CHECK();
-  tile_stats_kernel<<<blocks, 256, 0, stream>>>(plan->d_rowptr, t.d_tile_row, t.n_tiles, d_stats);
-  SBLAS_LAUNCH_CHECK();
   int32_t h_stats[2] = {0, 0};
-  SBLAS_CUDA(cudaMemcpyAsync(h_stats, d_stats, sizeof h_stats, cudaMemcpyDeviceToHost, stream));
-  SBLAS_CUDA(cudaStreamSynchronize(stream));
-  SBLAS_CUDA(cudaFree(d_stats));
+  const int blocks = (int)ceil_div(t.n_tiles + 1, 256);
+  auto build = [&]() -> int {  // any failure below releases the partial allocations
+    SBLAS_CUDA(cudaMalloc(&t.d_tile_row, sizeof(int32_t) * (size_t)(t.n_tiles + 1)));
+    SBLAS_CUDA(cudaMalloc(&t.d_tile_nnz, sizeof(int32_t) * (size_t)(t.n_tiles + 1)));
+    SBLAS_CUDA(cudaMalloc(&d_stats, 2 * sizeof(int32_t)));
+    SBLAS_CUDA(cudaMemsetAsync(d_stats, 0, 2 * sizeof(int32_t), stream));
+    tile_search_kernel<<<blocks, 256, 0, stream>>>(plan->d_rowptr, plan->rows, rw, T, t.n_tiles,
+                                                   t.d_tile_row, t.d_tile_nnz);
+    SBLAS_LAUNCH_CHECK();
+    tile_stats_kernel<<<blocks, 256, 0, stream>>>(plan->d_rowptr, t.d_tile_row, t.n_tiles, d_stats);
+    SBLAS_LAUNCH_CHECK();
+    SBLAS_CUDA(cudaMemcpyAsync(h_stats, d_stats, sizeof h_stats, cudaMemcpyDeviceToHost, stream));
+    SBLAS_CUDA(cudaStreamSynchronize(stream));
+    return 0;
+  };
+  const int brc = build();
+  if (d_stats) cudaFree(d_stats);
+  if (brc) {
+    if (t.d_tile_row) cudaFree(t.d_tile_row);
+    if (t.d_tile_nnz) cudaFree(t.d_tile_nnz);
+    return brc;
+  }
   t.max_tile_nnz = h_stats[0];
   t.max_tile_rows = h_stats[1];
   plan->tables.reserve(16);  // pointers handed out stay valid for the first 16 tables
@@ -178,6 +227,7 @@ int sblas_plan_destroy(sblasPlan_t p) {
   for (TileTable& t : p->tables) { cudaFree(t.d_tile_row); if (t.d_tile_nnz) cudaFree(t.d_tile_nnz); }
   if (p->d_split_scratch) cudaFree(p->d_split_scratch);
   rowblocks_free(p);
+  colpanels_free(p);
   cudaSetDevice(cur);
   delete p;
   return 0;

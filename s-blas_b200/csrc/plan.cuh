@@ -15,6 +15,8 @@
 
 #include "common.cuh"
 
+struct sblasPlan_st;
+
 namespace sblas {
 
 struct TileTable {
@@ -52,6 +54,20 @@ struct RowBlocks {
   int32_t max_tile_cols = 0;         // 0: no lists (unsorted rows, or not built)
 };
 
+// Column-panel mirror of A for gather-heavy SpMV (colpanel.cu): panel p = the nonzeros with a column in
+// [p*panel_cols, (p+1)*panel_cols), a CSR of its own; n = 0: not materialised.
+struct ColPanels {
+  int32_t n = 0;
+  int32_t panel_cols = 0;
+  bool is_f64 = true;
+  int32_t* d_rowptr = nullptr;   // [n][rows + 1] local row pointers of every panel
+  int32_t* d_colidx = nullptr;   // panel p at nnz_off[p] (a multiple of 4: 16-byte aligned)
+  void* d_val = nullptr;
+  void* d_part = nullptr;        // [rows] raw running row sums carried from pass to pass
+  std::vector<int64_t> nnz_off;  // [n + 1]
+  std::vector<sblasPlan_st*> sub;  // per panel: row statistics + tile tables
+};
+
 }  // namespace sblas
 
 struct sblasPlan_st {
@@ -66,6 +82,7 @@ struct sblasPlan_st {
   void* d_split_scratch = nullptr;
   size_t split_scratch_bytes = 0;
   sblas::RowBlocks rb;
+  sblas::ColPanels cp;
   // mean |first column of row r+1 - first column of row r| over a sample of rows (-1 = not measured yet):
   // ~1 for banded / stencil inputs, ~cols/nnz_per_row for random ones.  Measured lazily by the first AUTO SpMV
   // whose x does not fit L2 (spmv.cu, col_jump_kernel).
@@ -74,10 +91,35 @@ struct sblasPlan_st {
 
 namespace sblas {
 
+// Drops an ephemeral plan (plan == NULL calls) on every exit path of an op.
+struct EphemeralPlan {
+  sblasPlan_st* p = nullptr;
+  cudaStream_t st = nullptr;
+  ~EphemeralPlan() {
+    if (p) {
+      cudaStreamSynchronize(st);
+      sblas_plan_destroy(p);
+    }
+  }
+};
+
+// Residency of a persistent kernel, cached per (kernel, device, block, dynamic shared memory): the
+// cudaFuncSetAttribute / cudaOccupancyMaxActiveBlocksPerMultiprocessor / cudaDeviceGetAttribute calls cost
+// several microseconds of host time, which is visible beside a 70 us SpMV when made on every call.
+int kernel_residency(const void* kern, int block, size_t smem, int* per_sm, int* n_sm);
+
 // Finds or builds the tile table (row_weight, tile) of a plan.  Builds synchronise `stream`.
 int plan_get_table(sblasPlan_st* plan, cudaStream_t stream, int32_t row_weight, int32_t tile,
                    const TileTable** out);
 int plan_scratch(sblasPlan_st* plan, size_t bytes, void** out);
 void rowblocks_free(sblasPlan_st* plan);
+void colpanels_free(sblasPlan_st* plan);
+// spmv.cu: measures the plan's col_jump statistic when x is larger than ~L2 (one tiny kernel + a 16-byte copy,
+// synchronises `st`; cached) and says whether the input is gather-heavy (x does not stay in L2 and
+// consecutive rows look at unrelated parts of it)
+bool measure_gather_heavy(cudaStream_t st, sblasPlan_st* plan, const int32_t* rp, const int32_t* ci, int32_t rows,
+                          int32_t cols, size_t elem_size);
+// spmv.cu: builds the tile table the PIPE kernel will ask for (so that no SpMV call has to)
+int prepare_pipe_table(cudaStream_t st, sblasPlan_st* plan, bool* pipe_ok);
 
 }  // namespace sblas

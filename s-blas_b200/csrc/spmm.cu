@@ -88,6 +88,34 @@ __device__ __forceinline__ float4 vload_b(const float4* p, bool nol1) { return n
 __device__ __forceinline__ double vload_b(const double* p, bool nol1) { return nol1 ? ldg_stream(p) : __ldg(p); }
 __device__ __forceinline__ float vload_b(const float* p, bool nol1) { return nol1 ? ldg_stream(p) : __ldg(p); }
 
+__device__ __forceinline__ double vget(const double2& a, int e) { return e == 0 ? a.x : a.y; }
+__device__ __forceinline__ float vget(const float4& a, int e) { return e == 0 ? a.x : e == 1 ? a.y : e == 2 ? a.z : a.w; }
+__device__ __forceinline__ double vget(const double& a, int) { return a; }
+__device__ __forceinline__ float vget(const float& a, int) { return a; }
+
+// Fused epilogue of one lane: result columns [c0, c0 + VEC) of the row at element offset `off`.  A row's last
+// vector may be partial (k not a multiple of VEC): only columns < k are read and written then, so whatever the
+// caller keeps in C[.., k .. ld) survives (a sub-matrix view, or the padding of DenseMatrix's device mirror).
+template <typename T, int VEC>
+__device__ __forceinline__ void emit_row_slice(const MatSink<T>& sink, int64_t off, int c0,
+                                               const typename VecT<T, VEC>::type& acc) {
+  using V = typename VecT<T, VEC>::type;
+  if (VEC == 1 || c0 + VEC <= sink.k) {
+    const V cv = *reinterpret_cast<const V*>(sink.C + off);
+    const V res = vaxpby(sink.alpha, acc, sink.beta, cv);
+    *reinterpret_cast<V*>(sink.C + off) = res;
+    for (int d = 0; d < sink.out.n; ++d) *reinterpret_cast<V*>(sink.out.ptr[d] + off) = res;
+  } else {
+#pragma unroll
+    for (int e = 0; e < VEC; ++e)
+      if (c0 + e < sink.k) {
+        const T res = axpby_rn(sink.alpha, vget(acc, e), sink.beta, sink.C[off + e]);
+        sink.C[off + e] = res;
+        for (int d = 0; d < sink.out.n; ++d) sink.out.ptr[d][off + e] = res;
+      }
+  }
+}
+
 // ---- ROWMAJOR ---------------------------------------------------------------------------------
 // G lanes per A row, VEC elements per lane per column block, NB column blocks per lane:
 // covers k <= G*VEC*NB columns (larger k: the host loops over column panels).
@@ -169,11 +197,7 @@ spmm_rm_kernel(const int32_t* __restrict__ tile_row, const int32_t* __restrict__
           if (slot >= 0) {
             *reinterpret_cast<V*>(sink.carry + (int64_t)slot * sink.kpad + c0) = acc[nb];
           } else {
-            const int64_t off = (int64_t)r * sink.ldc + c0;
-            const V cv = *reinterpret_cast<const V*>(sink.C + off);
-            const V res = vaxpby(sink.alpha, acc[nb], sink.beta, cv);
-            *reinterpret_cast<V*>(sink.C + off) = res;
-            for (int d = 0; d < sink.out.n; ++d) *reinterpret_cast<V*>(sink.out.ptr[d] + off) = res;
+            emit_row_slice<T, VEC>(sink, (int64_t)r * sink.ldc + c0, c0, acc[nb]);
           }
         }
       }
@@ -250,11 +274,7 @@ spmm_rb_kernel(int64_t n_blockrows, const int32_t* __restrict__ blk_ptr, const i
           if (slot >= 0) {
             *reinterpret_cast<V*>(sink.carry + (int64_t)slot * sink.kpad + c0) = acc[r][nb];
           } else {
-            const int64_t off = row * sink.ldc + c0;
-            const V cv = *reinterpret_cast<const V*>(sink.C + off);
-            const V res = vaxpby(sink.alpha, acc[r][nb], sink.beta, cv);
-            *reinterpret_cast<V*>(sink.C + off) = res;
-            for (int d = 0; d < sink.out.n; ++d) *reinterpret_cast<V*>(sink.out.ptr[d] + off) = res;
+            emit_row_slice<T, VEC>(sink, row * sink.ldc + c0, c0, acc[r][nb]);
           }
         }
       }
@@ -602,18 +622,14 @@ static int launch_rbp_r(cudaStream_t st, const sblasPlan_st* plan, int NB, int l
 #undef SBLAS_RBP
   const size_t smem = smem_for(ns);
   SBLAS_CHECK(smem <= 200 * 1024, "spmm rowblock pipe: tile needs %zu bytes of shared memory", smem);
-  if (smem > 48 * 1024) SBLAS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   // experiment hooks: SBLAS_RBP_CARVEOUT = percent of the 256 KB L1/shared array given to shared memory,
   // SBLAS_RBP_PER_SM = resident CTAs per SM the persistent grid is sized for
   static const int env_carve = [] { const char* e = getenv("SBLAS_RBP_CARVEOUT"); return e ? atoi(e) : -1; }();
   static const int env_per_sm = [] { const char* e = getenv("SBLAS_RBP_PER_SM"); return e ? atoi(e) : 0; }();
   if (env_carve >= 0) cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, env_carve);
-  int per_sm = 0;
-  SBLAS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kRbpBlock, smem));
-  SBLAS_CHECK(per_sm >= 1, "spmm rowblock pipe: kernel does not fit an SM");
+  int per_sm = 0, n_sm = kNumSM;
+  if (int rr = kernel_residency(kern, kRbpBlock, smem, &per_sm, &n_sm)) return rr;
   if (env_per_sm > 0) per_sm = std::min(per_sm, env_per_sm);
-  int n_sm = kNumSM;
-  cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, plan->device);
   const int64_t n_tiles = ceil_div(rb.n_blockrows, W);
   const int grid = (int)std::min<int64_t>(n_tiles, (int64_t)n_sm * per_sm);
   const int2* cm = (const int2*)rb.d_colmask;
@@ -876,12 +892,8 @@ static int launch_rbt(cudaStream_t st, const sblasPlan_st* plan, int NB, const T
                              : (const void*)spmm_rbt_kernel<T, VEC, 2, R, EXACT>;
   const size_t smem = rbt_smem_bytes<T>(plan, NB);
   SBLAS_CHECK(smem > 0 && smem <= 220 * 1024, "spmm rowblock tileb: tile needs %zu bytes of shared memory", smem);
-  if (smem > 48 * 1024) SBLAS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  int per_sm = 0;
-  SBLAS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kRbpBlock, smem));
-  SBLAS_CHECK(per_sm >= 1, "spmm rowblock tileb: kernel does not fit an SM");
-  int n_sm = kNumSM;
-  cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, plan->device);
+  int per_sm = 0, n_sm = kNumSM;
+  if (int rr = kernel_residency(kern, kRbpBlock, smem, &per_sm, &n_sm)) return rr;
   const int64_t n_tiles = ceil_div(rb.n_blockrows, kRbpConsumers);
   const int grid = (int)std::min<int64_t>(n_tiles, (int64_t)n_sm * per_sm);
   const int2* cm = (const int2*)rb.d_colmask;
@@ -995,6 +1007,16 @@ static int launch_rm(cudaStream_t st, const TileTable* tt, int G, int NB, const 
   return 0;
 }
 
+// process-wide default arithmetic of SpMM: -1 = not decided yet (environment), 0 = FMA, 1 = exact
+static int g_spmm_exact = -1;
+static int spmm_exact_default() {
+  if (g_spmm_exact < 0) {
+    const char* e = getenv("SBLAS_EXACT");
+    g_spmm_exact = (e && atoi(e) != 0) ? 1 : 0;
+  }
+  return g_spmm_exact;
+}
+
 template <typename T>
 static int spmm_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, const int32_t* rp,
                      const int32_t* ci, const T* v, int32_t k, int32_t layout, const T* B,
@@ -1012,10 +1034,11 @@ static int spmm_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
   else
     SBLAS_CHECK(ldb >= cols && ldc >= rows, "spmm: col-major ld must be >= rows of the operand");
 
-  sblasPlan_st* eph = nullptr;
+  EphemeralPlan eph;  // released on every exit path
+  eph.st = st;
   if (!plan) {
-    if (sblas_plan_create_i32(st, rows, nnz, rp, &eph)) return 4;
-    plan = eph;
+    if (sblas_plan_create_i32(st, rows, nnz, rp, &eph.p)) return 4;
+    plan = eph.p;
   }
   SBLAS_CHECK(plan->rows == rows && plan->nnz == nnz, "spmm: plan does not match matrix");
   const int32_t tile = (o && o->tile > 0) ? o->tile : kSpmmDefaultTile;
@@ -1033,7 +1056,12 @@ static int spmm_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
   sink.flags = flags;
   sink.alpha = alpha;
   sink.beta = beta;
-  const bool exact = !(flags & SBLAS_FLAG_FMA);
+  // arithmetic: fused multiply-add by default (the north star grants fp64 <= 1e-12 / fp32 <= 1e-5 per row against
+  // |A||x| for reduction-order differences, and the FP64 pipe issues one DFMA where the exact mode needs DMUL +
+  // DADD: k = 256 banded 7.4 -> 6.2 ms); SBLAS_FLAG_EXACT (or SBLAS_EXACT=1 in the environment, for callers that
+  // go through the C++ headers, or
+  // sblas_set_spmm_exact(1)) keeps the separately rounded mul/add that is bit-identical to spmm.h:56-68
+  const bool exact = (flags & SBLAS_FLAG_EXACT) ? true : (flags & SBLAS_FLAG_FMA) ? false : spmm_exact_default() != 0;
 
   if (rc == 0 && layout == SBLAS_ROW_MAJOR) {
     constexpr int VF = Vec16<T>::N;
@@ -1096,7 +1124,6 @@ static int spmm_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
           rc = exact ? launch_rb<T, VF, true>(st, plan, std::min(NB, 4), B + c_off, ldb, ps)
                      : launch_rb<T, VF, false>(st, plan, std::min(NB, 4), B + c_off, ldb, ps);
       }
-      if (eph) { cudaStreamSynchronize(st); sblas_plan_destroy(eph); }
       return rc;
     }
     const int panel = 32 * VEC * 8;  // columns one launch covers at most
@@ -1141,10 +1168,6 @@ static int spmm_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
       }
     }
   }
-  if (eph) {
-    cudaStreamSynchronize(st);
-    sblas_plan_destroy(eph);
-  }
   return rc;
 }
 
@@ -1153,6 +1176,11 @@ static int spmm_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
 using namespace sblas;
 
 extern "C" {
+int sblas_set_spmm_exact(int on) {
+  const int prev = spmm_exact_default();
+  g_spmm_exact = on ? 1 : 0;
+  return prev;
+}
 int sblas_spmm_csr_f64(void* stream, int32_t rows, int32_t cols, int64_t nnz, const int32_t* rp,
                        const int32_t* ci, const double* v, int32_t k, int32_t layout,
                        const double* B, int64_t ldb, double* C, int64_t ldc, double alpha,

@@ -36,6 +36,13 @@ struct RowSink {
   int32_t rows;   // local row count
   int32_t flags;  // HEAD_PARTIAL | TAIL_PARTIAL
   T alpha, beta;
+  // column-panelled SpMV (colpanel.cu): the passes over the panels of A carry the RAW running row sums in
+  // `part`.  phase 0 = plain call; 1 = first panel (part = sum); 2 = middle panel (part = part (+) sum, the
+  // accumulation CONTINUES from the carried value); 3 = last panel (y = beta*y + alpha*(part (+) sum)).
+  // stage_src = what the PIPE kernel stages per row beside the tile: y (phase 0), nothing (1), part (2, 3).
+  T* part;
+  const T* stage_src;
+  int32_t phase;
 
   __device__ __forceinline__ void put(int32_t r, T sum) const {
     if ((flags & SBLAS_FLAG_HEAD_PARTIAL) && r == 0) { carry[0] = sum; return; }
@@ -44,11 +51,12 @@ struct RowSink {
     y[r] = res;
     for (int d = 0; d < out.n; ++d) out.ptr[d][r] = res;
   }
-  // same, with the old y[r] already staged by the caller (pipelined kernel)
-  __device__ __forceinline__ void put_y(int32_t r, T sum, T yold) const {
+  // same, with the row's staged value (old y[r]; in phases 2 / 3 the carried sum, which `sum` already continues)
+  __device__ __forceinline__ void put_y(int32_t r, T sum, T staged) const {
+    if (phase == 1 || phase == 2) { part[r] = sum; return; }
     if ((flags & SBLAS_FLAG_HEAD_PARTIAL) && r == 0) { carry[0] = sum; return; }
     if ((flags & SBLAS_FLAG_TAIL_PARTIAL) && r == rows - 1) { carry[4] = sum; return; }
-    T res = axpby_rn(alpha, sum, beta, yold);
+    T res = axpby_rn(alpha, sum, beta, phase == 3 ? y[r] : staged);
     y[r] = res;
     for (int d = 0; d < out.n; ++d) out.ptr[d][r] = res;
   }
@@ -282,6 +290,8 @@ struct PipeSink {
   const T* s_y;
   int32_t r0;
   __device__ __forceinline__ void put(int i, T sum) const { sink.put_y(r0 + i, sum, s_y[i]); }
+  // value the row's accumulation starts from: the sum carried over from the previous column panels
+  __device__ __forceinline__ T init(int i) const { return sink.phase >= 2 ? s_y[i] : T(0); }
 };
 
 // Rows of a staged tile: G lanes per row read (col, val) pairs from shared memory (consecutive
@@ -305,7 +315,7 @@ __device__ __forceinline__ void consume_rows(const int32_t* __restrict__ s_col,
     }
     s -= n0a;
     e -= n0a;
-    T sum = 0;
+    T sum = (valid && gl == 0) ? sink.init(i) : T(0);
     for (int j0 = s + gl; j0 < e; j0 += G * U) {
       T vv[U], xx[U];
 #pragma unroll
@@ -469,7 +479,8 @@ spmv_pipe_kernel(const int32_t* __restrict__ tile_row, const int32_t* __restrict
       cp_async_elem(st.val + (j - n0a), val + j);
     }
     for (int i2 = tid; i2 <= nrows; i2 += BLOCK) cp_async4(st.rp + i2, rowptr + r0 + i2);
-    for (int i2 = tid; i2 < nrows; i2 += BLOCK) cp_async_elem(st.y + i2, sink.y + r0 + i2);
+    if (sink.stage_src)
+      for (int i2 = tid; i2 < nrows; i2 += BLOCK) cp_async_elem(st.y + i2, sink.stage_src + r0 + i2);
     cp_async_mbar_arrive_noinc(bar);
   };
 
@@ -916,14 +927,15 @@ __global__ void col_jump_kernel(const int32_t* __restrict__ rowptr, const int32_
 
 constexpr size_t kGatherHeavyXBytes = 96u << 20;  // x beyond this does not stay in the 126 MB L2 beside the A stream
 
-// AUTO for gather-heavy inputs: when x does not fit L2 and consecutive rows look at unrelated parts of it
-// (uniform-random columns), every gather is a DRAM sector of its own and the kernel is bound by gathers in
-// flight, not by the A stream: sub-warp-per-row VECTOR keeps more of them in flight than PIPE's staged tiles
-// (16M x 32 uniform-random, fp64: 5.6 ms against 7.4 ms).  One tiny kernel + one 16-byte copy, once per plan.
-template <typename T>
-static bool gather_heavy(cudaStream_t st, sblasPlan_st* plan, const int32_t* rp, const int32_t* ci, int32_t rows,
-                         int32_t cols) {
-  if ((size_t)cols * sizeof(T) <= kGatherHeavyXBytes || rows < 4096 || plan->nnz == 0) return false;
+// Gather-heavy inputs: x does not fit L2 and consecutive rows look at unrelated parts of it (uniform-random
+// columns), so every gather is a DRAM sector of its own.  sync2gpu answers with the column-panel mirror
+// (colpanel.cu); without it AUTO takes the sub-warp-per-row VECTOR kernel, which keeps more gathers in
+// flight than PIPE's staged tiles (16M x 32 uniform-random, fp64: 5.6 ms against 7.4 ms).  The statistic
+// costs one tiny kernel + one 16-byte copy and a stream synchronisation, once per plan: sblas_plan_prepare_i32
+// / sblas_plan_build_colpanels_* take it at sync2gpu time so that no SpMV call has to.
+bool measure_gather_heavy(cudaStream_t st, sblasPlan_st* plan, const int32_t* rp, const int32_t* ci, int32_t rows,
+                          int32_t cols, size_t elem_size) {
+  if ((size_t)cols * elem_size <= kGatherHeavyXBytes || rows < 4096 || plan->nnz == 0) return false;
   if (plan->col_jump < 0.0) {
     void* scratch = nullptr;
     if (plan_scratch(plan, 64, &scratch)) return false;
@@ -956,6 +968,67 @@ static int set_smem_once(const void* fn, int bytes) {
   return 0;
 }
 
+// tile (merge items) PIPE uses for a plan: every row must fit a stage's staging buffer
+static int32_t pipe_tile_for(const sblasPlan_st* plan) {
+  return std::max<int32_t>(kSpmvPipeDefaultTile,
+                           std::min<int32_t>(2 * kSpmvPipeMaxRow, (2 * plan->max_row_nnz + 511) & ~511));
+}
+
+int prepare_pipe_table(cudaStream_t st, sblasPlan_st* plan, bool* pipe_ok) {
+  if (pipe_ok) *pipe_ok = plan->max_row_nnz <= kSpmvPipeMaxRow;
+  if (plan->max_row_nnz > kSpmvPipeMaxRow) return 0;  // SPLIT builds its own table
+  const TileTable* tt = nullptr;
+  return plan_get_table(plan, st, 1, pipe_tile_for(plan), &tt);
+}
+
+// PIPE launch on one CSR (the whole local matrix, or one column panel of it).  *fallback = the variant to take
+// instead when this input cannot be staged (unaligned col/val -> TILE, a row too long -> SPLIT).
+template <typename T>
+static int launch_pipe(cudaStream_t st, sblasPlan_st* plan, int32_t rows, int64_t nnz, const int32_t* rp,
+                       const int32_t* ci, const T* v, const T* x, const RowSink<T>& sink, const sblasOpts* o,
+                       bool auto_gather, int* fallback) {
+  *fallback = 0;
+  if (!(aligned16(ci) && aligned16(v))) { *fallback = SBLAS_SPMV_TILE; return 0; }
+  const int32_t tile = (o && o->tile > 0) ? o->tile : pipe_tile_for(plan);
+  const TileTable* tt = nullptr;
+  int rc = plan_get_table(plan, st, 1, tile, &tt);
+  if (rc) return rc;
+  const int32_t cap_nnz = (tt->max_tile_nnz + 8 + 3) & ~3;  // + head alignment slack
+  const int32_t cap_rows = tt->max_tile_rows + 1;
+  int stages = (o && o->stages > 0) ? o->stages : 2;
+  stages = std::min(std::max(stages, 2), 4);
+  auto smem_for = [&](int ns) { return (size_t)kPipeHeaderBytes + ns * pipe_stage_bytes<T>(cap_nnz, cap_rows); };
+  while (stages > 2 && smem_for(stages) > 110 * 1024) --stages;  // keep >= 2 CTAs per SM
+  if (smem_for(stages) > 200 * 1024) { *fallback = SBLAS_SPMV_SPLIT; return 0; }  // a row too long: cut rows instead
+  const size_t smem = smem_for(stages);
+  // lanes per row from the mean row length (one instantiation per launch keeps the
+  // kernel small: ~50 registers instead of 160 with an in-kernel switch)
+  const int G = (o && o->lanes > 0) ? o->lanes : pow2_lanes_pipe(rows ? (double)(nnz / rows) : 0.0);  // integer mean, as the per-tile rule of TILE
+  // tile order: CTA c takes tiles c, c+grid, ... (the resident CTAs sweep one contiguous window of A and
+  // share x through L2: best while x fits L2, c2 74 us against 86 us) or a run of consecutive tiles (the x
+  // lines of neighbouring tiles stay in the CTA's own L1: best when x is larger than L2 and rows are local,
+  // b32 1.376 -> 1.323 ms).  The part of x these rows touch is estimated as rows * col_jump elements (local
+  // rows advance col_jump columns per row; a row panel of a larger matrix touches only its own window of x);
+  // col_jump is only measured when the whole x exceeds 96 MB.  SBLAS_PIPE_CONSEC=0/1 overrides
+  // for experiments.  A template parameter: the strided instantiation is the kernel it always was.
+  static const int env_consec = [] { const char* e = getenv("SBLAS_PIPE_CONSEC"); return e ? atoi(e) : -1; }();
+  const bool big_window = plan->col_jump >= 0.0 && !auto_gather &&
+                          plan->col_jump * (double)rows * sizeof(T) > (double)kGatherHeavyXBytes;
+  const bool consec = env_consec >= 0 ? env_consec != 0 : big_window;
+  const void* kern = consec ? pipe_kernel_ptr<T, false, true>(stages, G) : pipe_kernel_ptr<T, false>(stages, G);
+  int per_sm = 0, n_sm = kNumSM;
+  if ((rc = kernel_residency(kern, kSpmvBlock, smem, &per_sm, &n_sm)) != 0) return rc;
+  const int grid = std::min<int>(tt->n_tiles, n_sm * per_sm);
+  SplitArgs<T> sp{};
+  void* args[] = {(void*)&tt->d_tile_row, (void*)&tt->d_tile_nnz, (void*)&tt->n_tiles, (void*)&rp,
+                  (void*)&ci, (void*)&v, (void*)&x, (void*)&sink, (void*)&cap_nnz,
+                  (void*)&cap_rows, (void*)&sp};
+  cudaError_t e = cudaLaunchKernel(kern, dim3(grid), dim3(kSpmvBlock), args, smem, st);
+  ++g_launches;
+  if (e != cudaSuccess) { set_error("spmv pipe launch: %s", cudaGetErrorString(e)); return 3; }
+  return 0;
+}
+
 template <typename T>
 static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, const int32_t* rp,
                      const int32_t* ci, const T* v, const T* x, T* y, T alpha, T beta,
@@ -974,74 +1047,58 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
   sink.flags = flags;
   sink.alpha = alpha;
   sink.beta = beta;
+  sink.part = nullptr;
+  sink.stage_src = y;
+  sink.phase = 0;
   int32_t tile = (o && o->tile > 0) ? o->tile : kSpmvDefaultTile;
-  sblasPlan_st* eph = nullptr;
+  EphemeralPlan eph;  // released on every exit path
+  eph.st = st;
   int variant = resolve_variant<T>(plan, o, tile);
   if (!plan && variant != SBLAS_SPMV_VECTOR) {
-    if (sblas_plan_create_i32(st, rows, nnz, rp, &eph)) return 4;
-    plan = eph;
+    if (sblas_plan_create_i32(st, rows, nnz, rp, &eph.p)) return 4;
+    plan = eph.p;
   }
   if (plan) SBLAS_CHECK(plan->rows == rows && plan->nnz == nnz, "spmv: plan does not match matrix");
+  const bool user_variant = o && o->variant != SBLAS_VARIANT_AUTO;
+  const bool have_panels = plan && plan->cp.n > 0 && plan->cp.is_f64 == (sizeof(T) == 8) &&
+                           (int64_t)cols <= (int64_t)plan->cp.n * plan->cp.panel_cols;
+  if (variant == SBLAS_SPMV_COLPANEL)
+    SBLAS_CHECK(have_panels, "spmv: SBLAS_SPMV_COLPANEL needs a plan with column panels of this value type (sblas_plan_build_colpanels_*)");
   bool auto_gather = false;
-  if (plan && variant == SBLAS_SPMV_PIPE && !(o && o->variant != SBLAS_VARIANT_AUTO) &&
-      gather_heavy<T>(st, plan, rp, ci, rows, cols)) {
+  if (!user_variant && have_panels) {
+    variant = SBLAS_SPMV_COLPANEL;
+  } else if (plan && variant == SBLAS_SPMV_PIPE && !user_variant &&
+             measure_gather_heavy(st, plan, rp, ci, rows, cols, sizeof(T))) {
     variant = SBLAS_SPMV_VECTOR;
     auto_gather = true;
   }
   const bool vec = aligned16(ci) && aligned16(v);
   int rc = 0;
-  if (variant == SBLAS_SPMV_PIPE && !(o && o->tile > 0))  // every row must fit a tile's staging buffer
-    tile = std::max<int32_t>(kSpmvPipeDefaultTile, std::min<int32_t>(2 * kSpmvPipeMaxRow, (2 * plan->max_row_nnz + 511) & ~511));
+  if (variant == SBLAS_SPMV_COLPANEL) {
+    // P passes of the PIPE kernel, one per column panel of the plan's mirror (colpanel.cu): pass p gathers
+    // only from x[p*W, (p+1)*W), which stays L2-resident while the panel streams by
+    const ColPanels& cp = plan->cp;
+    sblasOpts po;
+    if (o) { po = *o; po.tile = 0; }
+    for (int p = 0; p < cp.n && rc == 0; ++p) {
+      RowSink<T> ps = sink;
+      ps.part = (T*)cp.d_part;
+      ps.phase = cp.n == 1 ? 0 : p == 0 ? 1 : p == cp.n - 1 ? 3 : 2;
+      ps.stage_src = ps.phase == 0 ? y : ps.phase == 1 ? nullptr : (const T*)cp.d_part;
+      sblasPlan_st* sub = cp.sub[(size_t)p];
+      const int64_t off = cp.nnz_off[(size_t)p];
+      int fb = 0;
+      rc = launch_pipe<T>(st, sub, rows, sub->nnz, sub->d_rowptr, cp.d_colidx + off, (const T*)cp.d_val + off, x, ps,
+                          o ? &po : nullptr, false, &fb);
+      if (rc == 0 && fb != 0) { set_error("spmv: column panel %d cannot be staged by the PIPE kernel", p); rc = 5; }
+    }
+    return rc;
+  }
   if (variant == SBLAS_SPMV_PIPE) {
     // persistent TMA-staged tiles; needs 16-byte aligned col_idx / val (else: TILE)
-    const TileTable* tt = nullptr;
-    if (!vec) {
-      variant = SBLAS_SPMV_TILE;
-    } else if ((rc = plan_get_table(plan, st, 1, tile, &tt)) == 0) {
-      const int32_t cap_nnz = (tt->max_tile_nnz + 8 + 3) & ~3;  // + head alignment slack
-      const int32_t cap_rows = tt->max_tile_rows + 1;
-      int stages = (o && o->stages > 0) ? o->stages : 2;
-      stages = std::min(std::max(stages, 2), 4);
-      auto smem_for = [&](int ns) { return (size_t)kPipeHeaderBytes + ns * pipe_stage_bytes<T>(cap_nnz, cap_rows); };
-      while (stages > 2 && smem_for(stages) > 110 * 1024) --stages;  // keep >= 2 CTAs per SM
-      if (smem_for(stages) > 200 * 1024) {
-        variant = SBLAS_SPMV_SPLIT;  // a row too long for the staging buffers: cut rows instead
-      } else {
-        const int smem = (int)smem_for(stages);
-        // lanes per row from the mean row length (one instantiation per launch keeps the
-        // kernel small: ~50 registers instead of 160 with an in-kernel switch)
-        int G = (o && o->lanes > 0) ? o->lanes : pow2_lanes_pipe(rows ? (double)(nnz / rows) : 0.0);  // integer mean, as the per-tile rule of TILE
-        // tile order: CTA c takes tiles c, c+grid, ... (the resident CTAs sweep one contiguous window of A and
-        // share x through L2: best while x fits L2, c2 74 us against 86 us) or a run of consecutive tiles (the x
-        // lines of neighbouring tiles stay in the CTA's own L1: best when x is larger than L2 and rows are local,
-        // b32 1.376 -> 1.323 ms).  The part of x these rows touch is estimated as rows * col_jump elements (local
-        // rows advance col_jump columns per row; a row panel of a larger matrix touches only its own window of x);
-        // col_jump is only measured when the whole x exceeds 96 MB (gather_heavy).  SBLAS_PIPE_CONSEC=0/1 overrides
-        // for experiments.  A template parameter: the strided instantiation is the kernel it always was.
-        static const int env_consec = [] { const char* e = getenv("SBLAS_PIPE_CONSEC"); return e ? atoi(e) : -1; }();
-        const bool big_window = plan->col_jump >= 0.0 && !auto_gather &&
-                                plan->col_jump * (double)rows * sizeof(T) > (double)kGatherHeavyXBytes;
-        const bool consec = env_consec >= 0 ? env_consec != 0 : big_window;
-        const void* kern = consec ? pipe_kernel_ptr<T, false, true>(stages, G) : pipe_kernel_ptr<T, false>(stages, G);
-        int per_sm = 0;
-        if ((rc = set_smem_once<T>(kern, smem)) == 0) {
-          cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kSpmvBlock, smem);
-          if (e != cudaSuccess || per_sm < 1) { set_error("spmv pipe: occupancy query: %s", cudaGetErrorString(e)); rc = 1; }
-        }
-        if (rc == 0) {
-          int n_sm = kNumSM;
-          cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, plan->device);
-          const int grid = std::min<int>(tt->n_tiles, n_sm * per_sm);
-          SplitArgs<T> sp{};
-          void* args[] = {(void*)&tt->d_tile_row, (void*)&tt->d_tile_nnz, (void*)&tt->n_tiles, (void*)&rp,
-                          (void*)&ci, (void*)&v, (void*)&x, (void*)&sink, (void*)&cap_nnz,
-                          (void*)&cap_rows, (void*)&sp};
-          cudaError_t e = cudaLaunchKernel(kern, dim3(grid), dim3(kSpmvBlock), args, smem, st);
-          ++g_launches;
-          if (e != cudaSuccess) { set_error("spmv pipe launch: %s", cudaGetErrorString(e)); rc = 3; }
-        }
-      }
-    }
+    int fb = 0;
+    rc = launch_pipe<T>(st, plan, rows, nnz, rp, ci, v, x, sink, o, auto_gather, &fb);
+    if (rc == 0 && fb != 0) variant = fb;
   }
   if (rc == 0 && variant == SBLAS_SPMV_TILE) {
     const TileTable* tt = nullptr;
@@ -1072,11 +1129,17 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
       TileTable t;
       t.tile = tile;
       t.row_weight = -1;
+      t.d_tile_nnz = nullptr;  // the split table has no nnz column: windows follow from the merge diagonal
       t.n_tiles = (int32_t)ceil_div(std::max<int64_t>((int64_t)rows + nnz, 1), tile);
       SBLAS_CUDA(cudaMalloc(&t.d_tile_row, sizeof(int32_t) * (size_t)(t.n_tiles + 1)));
       split_search_kernel<<<(int)ceil_div(t.n_tiles + 1, 256), 256, 0, st>>>(rp, rows, nnz, tile,
                                                                            t.n_tiles, t.d_tile_row);
-      SBLAS_LAUNCH_CHECK();
+      ++g_launches;
+      if (cudaGetLastError() != cudaSuccess) {
+        cudaFree(t.d_tile_row);
+        set_error("spmv split: table build launch failed");
+        return 3;
+      }
       t.max_tile_nnz = tile;
       t.max_tile_rows = tile;
       plan->tables.reserve(16);
@@ -1098,18 +1161,13 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
         int stages = (o && o->stages > 0) ? std::min(std::max(o->stages, 2), 4) : 2;
         auto smem_for = [&](int ns) { return (size_t)kPipeHeaderBytes + ns * pipe_stage_bytes<T>(cap_nnz, cap_rows); };
         while (stages > 2 && smem_for(stages) > 110 * 1024) --stages;
-        const int smem = (int)smem_for(stages);
+        const size_t smem = smem_for(stages);
         int G = (o && o->lanes > 0) ? o->lanes : pow2_lanes_pipe(rows ? (double)(nnz / std::max<int64_t>(rows - plan->empty_rows, 1)) : 0.0);
         const void* kern = pipe_kernel_ptr<T, true>(stages, G);
-        int per_sm = 0;
+        int per_sm = 0, n_sm = kNumSM;
         if (smem > 200 * 1024) { set_error("spmv split: tile %d does not fit shared memory", tile); rc = 2; }
-        if (rc == 0 && (rc = set_smem_once<T>(kern, smem)) == 0) {
-          cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kSpmvBlock, smem);
-          if (e != cudaSuccess || per_sm < 1) { set_error("spmv split: occupancy query: %s", cudaGetErrorString(e)); rc = 1; }
-        }
+        if (rc == 0) rc = kernel_residency(kern, kSpmvBlock, smem, &per_sm, &n_sm);
         if (rc == 0) {
-          int n_sm = kNumSM;
-          cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, plan->device);
           const int grid = std::min<int>(tt->n_tiles, n_sm * per_sm);
           SplitArgs<T> sp{tile, rows, nnz, carry_out, head_val, head_row};
           const int32_t* no_nnz_table = nullptr;
@@ -1167,10 +1225,6 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
     set_error("spmv: unknown variant %d", variant);
     rc = 2;
   }
-  if (eph) {
-    cudaStreamSynchronize(st);
-    sblas_plan_destroy(eph);
-  }
   return rc;
 }
 
@@ -1189,6 +1243,15 @@ int sblas_spmv_csr_f32(void* stream, int32_t rows, int32_t cols, int64_t nnz, co
                        const int32_t* ci, const float* v, const float* x, float* y, float alpha,
                        float beta, sblasPlan_t plan, const sblasOpts* opts) {
   return spmv_impl<float>((cudaStream_t)stream, rows, cols, nnz, rp, ci, v, x, y, alpha, beta, plan, opts);
+}
+
+int sblas_plan_prepare_i32(void* stream, sblasPlan_t p, const int32_t* d_colidx, int32_t cols, int32_t elem_size) {
+  SBLAS_CHECK(p && (p->nnz == 0 || d_colidx) && cols >= 0 && (elem_size == 4 || elem_size == 8), "plan_prepare: bad arguments");
+  if (p->rows == 0) return 0;
+  cudaStream_t st = (cudaStream_t)stream;
+  measure_gather_heavy(st, p, p->d_rowptr, d_colidx, p->rows, cols, (size_t)elem_size);
+  bool ok = false;
+  return prepare_pipe_table(st, p, &ok);
 }
 
 int sblas_plan_col_jump(sblasPlan_t p, double* out) {

@@ -209,7 +209,30 @@ class RowSplitOp:
             for w in works:
                 w.wait()
 
+    def check(self):
+        """Raises if a device-side barrier of this op ever timed out (its status word is sticky): the
+        replica of y / C is then INCOMPLETE — a peer was more than SBLAS_BARRIER_TIMEOUT_MS late (first-call
+        plan build, a host stall, a profiler serialising the ranks).  Synchronises the device."""
+        st = getattr(self, "status", None)
+        if st is None:
+            return
+        bad = int(st.item())
+        if bad != 0:
+            raise RuntimeError("sblas peer barrier: rank %d timed out waiting for rank %d; the replicated "
+                               "output of this and later steps is incomplete" % (self.rank, bad - 1))
+
+    def synchronize(self):
+        """Host synchronisation point: waits for the device and verifies the barrier status."""
+        import torch
+        torch.cuda.synchronize()
+        self.check()
+
     def __call__(self, xB, out, alpha, beta):
         self.compute(xB, out, alpha, beta)
         self.exchange(out)
+        # the first step is where a rank can be late (lazy module load, plan tables): verify it before the
+        # caller can consume the result; afterwards at synchronize() / check(), and every 64th call
+        self._calls = getattr(self, "_calls", 0) + 1
+        if self._calls == 1 or self._calls % 64 == 0:
+            self.check()
         return out

@@ -159,6 +159,30 @@ class Plan:
             check(fn(stream_ptr(stream), self.handle, vp(colidx), vp(val), C.c_int32(R)), "plan_build_rowblocks")
         return self.rowblock_stats()
 
+    def prepare(self, colidx, cols, elem_size, stream=None):
+        """sblas_plan_prepare_i32: col_jump statistic + the staged kernel's tile table now, so that no SpMV
+        call on this plan synchronises (what CsrSparseMatrix::sync2gpu does)."""
+        import torch
+        with torch.cuda.device(colidx.device):
+            check(lib().sblas_plan_prepare_i32(stream_ptr(stream), self.handle, vp(colidx), C.c_int32(cols),
+                                               C.c_int32(elem_size)), "plan_prepare")
+        return self
+
+    def build_colpanels(self, colidx, val, cols, n_panels=0, stream=None):
+        """Column-panel mirror of A for gather-heavy SpMV (sblas_plan_build_colpanels_*); n_panels = 0: only
+        when it pays.  Returns (n_panels, panel_cols), (0, 0) when no mirror was built."""
+        import torch
+        fn = getattr(lib(), "sblas_plan_build_colpanels_" + _sfx(val.dtype))
+        with torch.cuda.device(val.device):
+            check(fn(stream_ptr(stream), self.handle, vp(colidx), vp(val), C.c_int32(cols), C.c_int32(n_panels)),
+                  "plan_build_colpanels")
+        return self.colpanel_stats()
+
+    def colpanel_stats(self):
+        n, w = C.c_int32(), C.c_int32()
+        check(lib().sblas_plan_colpanel_stats(self.handle, C.byref(n), C.byref(w)), "plan_colpanel_stats")
+        return int(n.value), int(w.value)
+
     def rowblock_stats(self):
         R, nb, fill = C.c_int32(), C.c_int64(), C.c_double()
         check(lib().sblas_plan_rowblock_stats(self.handle, C.byref(R), C.byref(nb), C.byref(fill)),
@@ -211,6 +235,12 @@ def spmm(rowptr, colidx, val, k, layout, B, ldb, Cm, ldc, alpha, beta, cols, pla
              C.c_int64(ldc), _scalar(val.dtype, alpha), _scalar(val.dtype, beta), _h(plan),
              C.byref(opts) if opts is not None else None), "spmm")
     return Cm
+
+
+def set_spmm_exact(on):
+    """Process-wide default arithmetic of SpMM (sblas_set_spmm_exact): True = separately rounded mul/add,
+    bit-identical to spmm.h:56-68; False = fused multiply-add.  Returns the previous setting."""
+    return bool(lib().sblas_set_spmm_exact(C.c_int(1 if on else 0)))
 
 
 def axpby(v0, v1, alpha, beta, stream=None):

@@ -9,6 +9,16 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(autouse=True)
+def _exact_spmm(sblas):
+    """These tests prove bit-identity with the reference's CPU loops: SpMM runs with separately rounded
+    mul/add (sblas_set_spmm_exact).  The default fused multiply-add arithmetic is covered by the
+    tolerance tests, which opt out with SBLAS_FLAG_FMA or switch the default back."""
+    prev = sblas.kernels.set_spmm_exact(True)
+    yield
+    sblas.kernels.set_spmm_exact(prev)
+
+
 def _bound(oracle, A, x, alpha, beta, y0):
     return abs(alpha) * oracle.absrow_spmv(A.csrRowPtr, A.csrColIdx, A.csrVal, x) + np.abs(beta * y0) + 1e-300
 

@@ -9,6 +9,16 @@ import synth_ref as SR
 
 pytestmark = pytest.mark.gpu
 
+
+@pytest.fixture(autouse=True)
+def _exact_spmm(sblas):
+    """These tests prove bit-identity with the reference's CPU loops: SpMM runs with separately rounded
+    mul/add (sblas_set_spmm_exact).  The default fused multiply-add arithmetic is covered by the
+    tolerance tests, which opt out with SBLAS_FLAG_FMA or switch the default back."""
+    prev = sblas.kernels.set_spmm_exact(True)
+    yield
+    sblas.kernels.set_spmm_exact(prev)
+
 TOL = {np.dtype(np.float64): 1e-12, np.dtype(np.float32): 1e-5}
 
 
@@ -397,6 +407,89 @@ def test_spmm_fma_flag_within_tolerance(sblas, dev, oracle):
     for n in range(0, k, 9):
         b = _row_bound(oracle, rp, ci, v, Bc[n * w:(n + 1) * w], 1.0, 1.0, C0c[n * h:(n + 1) * h])
         _check(got[n * h:(n + 1) * h], ref[n * h:(n + 1) * h], b, np.float64)
+
+
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+@pytest.mark.parametrize("k", [64, 256])
+@pytest.mark.parametrize("variant", ["auto_csr", "rowmajor", "colmajor", "rowblock", "rowblock_pipe", "rowblock_tileb"])
+def test_spmm_default_arithmetic_within_tolerance(sblas, dev, oracle, dtype, k, variant):
+    """The DEFAULT arithmetic of SpMM is fused multiply-add: every kernel variant, k = 64
+    and 256, stays within the north star's per-row bound (fp64 1e-12, fp32 1e-5, relative to |A||B|), and the
+    default really is FMA (it differs from the exact result somewhere, and equals the SBLAS_FLAG_FMA run)."""
+    import torch
+    K = sblas.kernels
+    rng = np.random.default_rng(k + len(variant))
+    h = w = 640
+    rp, ci, v = _banded_csr(rng, h, 24, dtype, jitter=0.1)
+    Bc, C0c = rng.random(w * k).astype(dtype), rng.random(h * k).astype(dtype)
+    alpha, beta = dtype(1.25), dtype(-0.75)
+    ref = _spmm_ref(oracle, rp, ci, v, k, Bc, C0c, alpha, beta)
+    drp, dci, dv = (_t(dev, a) for a in (rp, ci, v))
+    plan = K.Plan(drp, len(ci))
+    var = {"auto_csr": 0, "rowmajor": sblas.SPMM_ROWMAJOR, "colmajor": sblas.SPMM_COLMAJOR, "rowblock": sblas.SPMM_ROWBLOCK,
+           "rowblock_pipe": sblas.SPMM_ROWBLOCK_PIPE, "rowblock_tileb": sblas.SPMM_ROWBLOCK_TILEB}[variant]
+    if variant.startswith("rowblock"):
+        plan.build_rowblocks(dci, dv, R=-4)
+    cm = variant == "colmajor"
+
+    def run(flags):
+        if cm:
+            dB, dC = _t(dev, Bc), _t(dev, C0c)
+            K.spmm(drp, dci, dv, k, sblas.COL_MAJOR, dB, w, dC, h, alpha, beta, w, plan=plan,
+                   opts=sblas.make_opts(variant=var, flags=flags))
+            return dC.cpu().numpy()
+        dB, dC = _t(dev, _to_rm(Bc, w, k, k)), _t(dev, _to_rm(C0c, h, k, k))
+        K.spmm(drp, dci, dv, k, sblas.ROW_MAJOR, dB, k, dC, k, alpha, beta, w, plan=plan,
+               opts=sblas.make_opts(variant=var, flags=flags))
+        return _from_rm(dC.cpu().numpy(), h, k, k)
+
+    prev = K.set_spmm_exact(False)          # the library's initial default
+    try:
+        got_default = run(0)
+    finally:
+        K.set_spmm_exact(prev)
+    got_fma, got_exact = run(sblas.FLAG_FMA), run(sblas.FLAG_EXACT)
+    torch.cuda.synchronize()
+    assert np.array_equal(got_default, got_fma)
+    if not cm:      # one lane per (row, column) in CSR order; the col-major kernel shuffles-reduces lanes
+        assert np.array_equal(got_exact, ref)
+    assert not np.array_equal(got_default, got_exact), "default arithmetic is not FMA"
+    for n in range(0, k, max(1, k // 9)):
+        b = _row_bound(oracle, rp, ci, v, Bc[n * w:(n + 1) * w], alpha, beta, C0c[n * h:(n + 1) * h])
+        _check(got_default[n * h:(n + 1) * h], ref[n * h:(n + 1) * h], b, dtype)
+
+
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+@pytest.mark.parametrize("k", [1, 3, 5, 9, 66])
+@pytest.mark.parametrize("rowblock", [False, True])
+def test_spmm_leaves_padding_columns_alone(sblas, dev, oracle, dtype, k, rowblock):
+    """ADVICE r1 (spmm.cu vector path): with k not a multiple of the 16-byte vector and ld >= roundup(k), the
+    columns [k, ld) of C (a neighbouring sub-matrix, or padding) must not be touched — in C or in a replica."""
+    import torch
+    K = sblas.kernels
+    rng = np.random.default_rng(k)
+    h, w = 333, 257
+    rp, ci, v = _rand_csr(rng, h, w, 9, 0.1, None, dtype)
+    vec = 16 // np.dtype(dtype).itemsize
+    ld = (k + vec - 1) // vec * vec + vec          # a partial vector AND a whole untouched one
+    Bc, C0c = rng.random(w * k).astype(dtype), rng.random(h * k).astype(dtype)
+    ref = _spmm_ref(oracle, rp, ci, v, k, Bc, C0c, dtype(2.0), dtype(0.5))
+    B = rng.random((w, ld)).astype(dtype)          # garbage (not zeros) behind column k of B too
+    B[:, :k] = Bc.reshape(k, w).T
+    C0 = np.full((h, ld), -7.0, dtype)
+    C0[:, :k] = C0c.reshape(k, h).T
+    drp, dci, dv = (_t(dev, a) for a in (rp, ci, v))
+    plan = K.Plan(drp, len(ci))
+    if rowblock:
+        plan.build_rowblocks(dci, dv, R=-4)
+    dB, dC, dR = _t(dev, B.reshape(-1)), _t(dev, C0.reshape(-1)), _t(dev, np.full(h * ld, -9.0, dtype))
+    K.spmm(drp, dci, dv, k, sblas.ROW_MAJOR, dB, ld, dC, ld, 2.0, 0.5, w, plan=plan,
+           opts=sblas.make_opts(variant=sblas.SPMM_ROWBLOCK if rowblock and k >= 16 * vec else 0, replicas=[dR.data_ptr()]))
+    torch.cuda.synchronize()
+    got, rep = dC.cpu().numpy().reshape(h, ld), dR.cpu().numpy().reshape(h, ld)
+    assert np.array_equal(np.ascontiguousarray(got[:, :k].T).reshape(-1), ref)
+    assert np.all(got[:, k:] == -7.0), "columns >= k of C were overwritten"
+    assert np.array_equal(rep[:, :k], got[:, :k]) and np.all(rep[:, k:] == -9.0), "columns >= k of the replica were overwritten"
 
 
 @pytest.mark.parametrize("k", [64, 256, 9])

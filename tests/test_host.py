@@ -130,6 +130,48 @@ def test_mtx_loader_parallel_is_order_preserving(sblas, oracle, tmp_path, kind):
     sblas.kernels.read_mtx(str(p), threads=0)
 
 
+def test_mtx_loader_size_line_forms(sblas, oracle, tmp_path):
+    """The size line read as mm_read_mtx_crd_size reads it (mmio.h:338-366): an indented comment or a
+    blank line before it, a fourth token on it (dropped with the line), and garbage instead of it."""
+    head = "%%MatrixMarket matrix coordinate real general\n% c\n"
+    body = "1 1 1.5\n3 2 -2.0\n"
+    forms = {
+        "indent": head + "  % indented comment\n3 3 2\n" + body,
+        "blank": head + "\n3 3 2\n" + body,
+        "fourth": head + "3 3 2 7\n" + body,
+        "plain": head + "3 3 2\n" + body,
+    }
+    want = None
+    for name, txt in forms.items():
+        p = tmp_path / (name + ".mtx")
+        p.write_text(txt)
+        got = sblas.kernels.read_mtx(str(p), threads=2)
+        assert got[0] == 3 and got[1] == 3 and len(got[4]) == 2, name
+        ref = oracle.read_mtx(str(p))
+        for x, y in zip(got[2:], ref[2:]):
+            assert np.array_equal(x, y), name
+        if want is None:
+            want = got
+        for x, y in zip(got[2:], want[2:]):
+            assert np.array_equal(x, y), name
+    bad = tmp_path / "bad.mtx"
+    bad.write_text(head + "three 3 2\n" + body)
+    with pytest.raises(sblas.SblasError):
+        sblas.kernels.read_mtx(str(bad))
+
+
+def test_mtx_loader_size_line_forms_reference(sblas, reference, tmp_path):
+    head = "%%MatrixMarket matrix coordinate real general\n"
+    body = "1 1 1.5\n3 2 -2.0\n"
+    for name, txt in {"indent": head + " % x\n3 3 2\n" + body, "fourth": head + "3 3 2 7\n" + body}.items():
+        p = tmp_path / (name + ".mtx")
+        p.write_text(txt)
+        a, b = sblas.kernels.read_mtx(str(p)), reference.read_mtx(str(p))
+        assert a[0] == b[0] and a[1] == b[1], name
+        for x, y in zip(a[2:], b[2:]):
+            assert np.array_equal(x, y), name
+
+
 def test_mtx_loader_short_file_is_an_error(sblas, tmp_path):
     p = tmp_path / "short.mtx"
     p.write_text("%%MatrixMarket matrix coordinate real general\n3 3 4\n1 1 1.0\n2 2 2.0\n3 3\n")
