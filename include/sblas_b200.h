@@ -328,6 +328,22 @@ SBLAS_API int sblas_dense_download_f64(int gpu, const double* d, int64_t ld, int
                                        int64_t dim, int32_t dev_layout, double* h);
 SBLAS_API int sblas_dense_download_f32(int gpu, const float* d, int64_t ld, int64_t second,
                                        int64_t dim, int32_t dev_layout, float* h);
+/* The same two moves for a caller that re-sends a dense operand on every step (what a solver loop around
+ * sblas_spmm_csr_v2 does with B.sync2gpu / C.sync2cpu, spmm_test.cu:68-84), streamed and allocation-free:
+ * rows [r0, r0 + nr) of the col-major HOST matrix h (element (r, n) at h[n*h_ld + r], k columns; pinned memory
+ * for real overlap) <-> the row-major DEVICE block d (element (r - r0, n) at d[(r - r0)*ld + n]) on the current
+ * device.  Work is enqueued on `stream`: the PCIe copy of one row chunk overlaps the layout conversion of the
+ * previous one (a per-device helper stream per direction, so uploads and downloads overlap too), nothing is
+ * allocated per call and nothing synchronises; after a download, `stream` completes only when the bytes are on
+ * the host. */
+SBLAS_API int sblas_dense_upload_rows_f64(void* stream, const double* h, int64_t h_ld, int64_t r0, int64_t nr,
+                                          int32_t k, double* d_dst, int64_t ld);
+SBLAS_API int sblas_dense_upload_rows_f32(void* stream, const float* h, int64_t h_ld, int64_t r0, int64_t nr,
+                                          int32_t k, float* d_dst, int64_t ld);
+SBLAS_API int sblas_dense_download_rows_f64(void* stream, const double* d_src, int64_t ld, int64_t nr, int32_t k,
+                                            double* h, int64_t h_ld, int64_t r0);
+SBLAS_API int sblas_dense_download_rows_f32(void* stream, const float* d_src, int64_t ld, int64_t nr, int32_t k,
+                                            float* h, int64_t h_ld, int64_t r0);
 /* Managed memory of the matrix_um.h variants: cudaMallocManaged (matrix_um.h:60-75),
  * cudaMemAdvise / cudaMemPrefetchAsync (matrix_um.h:529-614).  gpu = -1 means the CPU. */
 enum {

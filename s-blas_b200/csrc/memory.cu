@@ -9,6 +9,8 @@
 // `gpu` is always a LOGICAL GPU ordinal (sblas_device_of).
 #include <stdlib.h>
 
+#include <algorithm>
+
 #include "common.cuh"
 
 namespace sblas {
@@ -99,10 +101,115 @@ static int dense_download(int gpu, const T* d_src, int64_t ld, int64_t second, i
   return 0;
 }
 
+// ---- streamed sync2gpu / sync2cpu of a row range (caller-owned device storage) -----------------------
+// DenseMatrix::sync2gpu / sync2cpu move a col-major host operand (matrix.h:541-570, :595-612); the device
+// keeps it row-major (see dense_upload above).  These variants are what a caller that re-sends B / C on
+// every step uses: no allocation, no synchronisation, and the PCIe copy of chunk i+1 overlaps the layout
+// conversion of chunk i.  A chunk is a range of rows: k pieces of (rows * sizeof(T)) contiguous bytes on
+// the host, one strided DMA (cudaMemcpy2DAsync) into a staging buffer [k x rows], then the transpose kernel
+// into the row-major destination.  Copies run on a per-device helper stream (one per direction, so H2D and
+// D2H overlap on the full-duplex link), conversions on the caller's stream; events order the two.
+struct XferCtx {
+  cudaStream_t copy = nullptr;
+  void* stage[2] = {nullptr, nullptr};
+  cudaEvent_t ready[2] = {nullptr, nullptr}, free_[2] = {nullptr, nullptr}, done = nullptr;
+  unsigned turn = 0;
+};
+constexpr size_t kXferStageBytes = 128u << 20;
+static XferCtx g_up[SBLAS_MAX_GPU * 4], g_down[SBLAS_MAX_GPU * 4];  // indexed by CUDA device
+
+static int xfer_get(XferCtx* table, XferCtx** out) {
+  int dev = 0;
+  SBLAS_CUDA(cudaGetDevice(&dev));
+  SBLAS_CHECK(dev >= 0 && dev < SBLAS_MAX_GPU * 4, "device ordinal %d out of range", dev);
+  XferCtx& c = table[dev];
+  if (!c.copy) {
+    SBLAS_CUDA(cudaStreamCreateWithFlags(&c.copy, cudaStreamNonBlocking));
+    for (int b = 0; b < 2; ++b) {
+      SBLAS_CUDA(cudaMalloc(&c.stage[b], kXferStageBytes));
+      SBLAS_CUDA(cudaEventCreateWithFlags(&c.ready[b], cudaEventDisableTiming));
+      SBLAS_CUDA(cudaEventCreateWithFlags(&c.free_[b], cudaEventDisableTiming));
+    }
+    SBLAS_CUDA(cudaEventCreateWithFlags(&c.done, cudaEventDisableTiming));
+  }
+  *out = &c;
+  return 0;
+}
+
+template <typename T>
+static int transpose_on(cudaStream_t st, const T* in, int64_t in_ld, int64_t n_major, int64_t n_minor, T* out, int64_t out_ld) {
+  return sizeof(T) == 8 ? sblas_transpose_f64(st, (const double*)in, in_ld, n_major, n_minor, (double*)out, out_ld)
+                        : sblas_transpose_f32(st, (const float*)in, in_ld, n_major, n_minor, (float*)out, out_ld);
+}
+
+template <typename T>
+static int upload_rows(cudaStream_t st, const T* h, int64_t h_ld, int64_t r0, int64_t nr, int32_t k, T* d_dst, int64_t ld) {
+  SBLAS_CHECK(nr >= 0 && k >= 0 && h_ld >= 0 && r0 >= 0 && ld >= k, "dense_upload_rows: bad arguments");
+  if (nr == 0 || k == 0) return 0;
+  SBLAS_CHECK(h && d_dst, "dense_upload_rows: null pointer");
+  XferCtx* c = nullptr;
+  if (xfer_get(g_up, &c)) return 1;
+  const int64_t chunk = std::max<int64_t>(1, (int64_t)(kXferStageBytes / sizeof(T)) / k);
+  for (int64_t r = 0; r < nr; r += chunk) {
+    const int64_t cr = std::min(chunk, nr - r);
+    const int b = (int)(c->turn++ & 1u);
+    SBLAS_CUDA(cudaStreamWaitEvent(c->copy, c->free_[b], 0));   // the conversion that last read this buffer
+    SBLAS_CUDA(cudaMemcpy2DAsync(c->stage[b], (size_t)cr * sizeof(T), h + r0 + r, (size_t)h_ld * sizeof(T),
+                                 (size_t)cr * sizeof(T), (size_t)k, cudaMemcpyHostToDevice, c->copy));
+    SBLAS_CUDA(cudaEventRecord(c->ready[b], c->copy));
+    SBLAS_CUDA(cudaStreamWaitEvent(st, c->ready[b], 0));
+    if (int rc = transpose_on<T>(st, (const T*)c->stage[b], cr, k, cr, d_dst + r * ld, ld)) return rc;
+    SBLAS_CUDA(cudaEventRecord(c->free_[b], st));
+  }
+  return 0;
+}
+
+template <typename T>
+static int download_rows(cudaStream_t st, const T* d_src, int64_t ld, int64_t nr, int32_t k, T* h, int64_t h_ld, int64_t r0) {
+  SBLAS_CHECK(nr >= 0 && k >= 0 && h_ld >= 0 && r0 >= 0 && ld >= k, "dense_download_rows: bad arguments");
+  if (nr == 0 || k == 0) return 0;
+  SBLAS_CHECK(h && d_src, "dense_download_rows: null pointer");
+  XferCtx* c = nullptr;
+  if (xfer_get(g_down, &c)) return 1;
+  const int64_t chunk = std::max<int64_t>(1, (int64_t)(kXferStageBytes / sizeof(T)) / k);
+  for (int64_t r = 0; r < nr; r += chunk) {
+    const int64_t cr = std::min(chunk, nr - r);
+    const int b = (int)(c->turn++ & 1u);
+    SBLAS_CUDA(cudaStreamWaitEvent(st, c->free_[b], 0));        // the copy that last drained this buffer
+    if (int rc = transpose_on<T>(st, d_src + r * ld, ld, cr, k, (T*)c->stage[b], cr)) return rc;
+    SBLAS_CUDA(cudaEventRecord(c->ready[b], st));
+    SBLAS_CUDA(cudaStreamWaitEvent(c->copy, c->ready[b], 0));
+    SBLAS_CUDA(cudaMemcpy2DAsync(h + r0 + r, (size_t)h_ld * sizeof(T), c->stage[b], (size_t)cr * sizeof(T),
+                                 (size_t)cr * sizeof(T), (size_t)k, cudaMemcpyDeviceToHost, c->copy));
+    SBLAS_CUDA(cudaEventRecord(c->free_[b], c->copy));
+  }
+  // the caller's stream completes only when the last bytes are on the host
+  SBLAS_CUDA(cudaEventRecord(c->done, c->copy));
+  SBLAS_CUDA(cudaStreamWaitEvent(st, c->done, 0));
+  return 0;
+}
+
 }  // namespace sblas
 
 using namespace sblas;
 extern "C" {
+
+int sblas_dense_upload_rows_f64(void* stream, const double* h, int64_t h_ld, int64_t r0, int64_t nr, int32_t k,
+                                double* d_dst, int64_t ld) {
+  return upload_rows<double>((cudaStream_t)stream, h, h_ld, r0, nr, k, d_dst, ld);
+}
+int sblas_dense_upload_rows_f32(void* stream, const float* h, int64_t h_ld, int64_t r0, int64_t nr, int32_t k,
+                                float* d_dst, int64_t ld) {
+  return upload_rows<float>((cudaStream_t)stream, h, h_ld, r0, nr, k, d_dst, ld);
+}
+int sblas_dense_download_rows_f64(void* stream, const double* d_src, int64_t ld, int64_t nr, int32_t k, double* h,
+                                  int64_t h_ld, int64_t r0) {
+  return download_rows<double>((cudaStream_t)stream, d_src, ld, nr, k, h, h_ld, r0);
+}
+int sblas_dense_download_rows_f32(void* stream, const float* d_src, int64_t ld, int64_t nr, int32_t k, float* h,
+                                  int64_t h_ld, int64_t r0) {
+  return download_rows<float>((cudaStream_t)stream, d_src, ld, nr, k, h, h_ld, r0);
+}
 
 int sblas_host_alloc(size_t bytes, void** p) {
   SBLAS_CHECK(p, "host_alloc: null out pointer");

@@ -267,6 +267,24 @@ def transpose(src, in_ld, n_major, n_minor, dst, out_ld, stream=None):
     return dst
 
 
+def dense_upload_rows(h, h_ld, r0, nr, k, d_dst, ld, stream=None):
+    """sblas_dense_upload_rows_*: rows [r0, r0+nr) of the col-major host tensor h (pinned) -> row-major device
+    block d_dst [nr x ld], streamed on `stream` (copy of chunk i+1 overlaps the conversion of chunk i)."""
+    fn = getattr(lib(), "sblas_dense_upload_rows_" + _sfx(d_dst.dtype))
+    check(fn(stream_ptr(stream), vp(h), C.c_int64(h_ld), C.c_int64(r0), C.c_int64(nr), C.c_int32(k), vp(d_dst),
+             C.c_int64(ld)), "dense_upload_rows")
+    return d_dst
+
+
+def dense_download_rows(d_src, ld, nr, k, h, h_ld, r0, stream=None):
+    """sblas_dense_download_rows_*: row-major device block d_src [nr x ld] -> rows [r0, r0+nr) of the col-major
+    host tensor h; `stream` completes when the bytes are on the host."""
+    fn = getattr(lib(), "sblas_dense_download_rows_" + _sfx(d_src.dtype))
+    check(fn(stream_ptr(stream), vp(d_src), C.c_int64(ld), C.c_int64(nr), C.c_int32(k), vp(h), C.c_int64(h_ld),
+             C.c_int64(r0)), "dense_download_rows")
+    return h
+
+
 def carry_fixup(rows, first, last, carry, k, layout, out, ld, alpha, beta, stream=None):
     rows, first, last = (np.ascontiguousarray(a, np.int32) for a in (rows, first, last))
     fn = getattr(lib(), "sblas_carry_fixup_" + _sfx(out.dtype))

@@ -22,6 +22,14 @@ def test_algorithmic_bytes_match_survey_8d():
     assert round(bench.gather_bytes("spmm", 1 << 24, 1 << 24, 1 << 29, 64, 8) / 1e9, 1) == 298.6
 
 
+def test_default_workload_is_the_north_star_config():
+    """BENCH / SCALE measure configs[2] (16M x 32 uniform, fp64 SpMM k=64, method 2) at every N."""
+    assert bench.DEFAULT_WORKLOAD == "c3"
+    cfgs = json.load(open(os.path.join(ROOT, "BASELINE.json")))["configs"]
+    assert "16M rows" in cfgs[2] and "k=64" in cfgs[2] and "method 2" in cfgs[2]
+    assert set(bench.OTHERS_N1) == {"c2", "c3v", "c4", "c5"} and set(bench.OTHERS_NX) == {"c4", "c5"}
+
+
 def test_workload_table_names_the_baseline_configs():
     cfgs = json.load(open(os.path.join(ROOT, "BASELINE.json")))["configs"]
     wl = bench.WORKLOADS

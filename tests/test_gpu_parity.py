@@ -641,6 +641,96 @@ def test_spmv_auto_gather_heavy(sblas, dev, oracle):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+@pytest.mark.parametrize("mat", ["short", "mid", "long", "empty_tail", "tiny"])
+@pytest.mark.parametrize("panels", [1, 2, 3, 7, 32])
+def test_spmv_column_panels(sblas, dev, oracle, dtype, mat, panels):
+    """SBLAS_SPMV_COLPANEL (colpanel.cu): one PIPE pass per column panel, the raw running row sums carried from
+    pass to pass.  Within the row tolerance for every shape; with one lane per row (lanes = 1) and ascending
+    columns the accumulation order is the CPU loop's, so the result is bit-identical to spmv.h:24-30."""
+    import torch
+    K = sblas.kernels
+    rng = np.random.default_rng(panels * 31 + len(mat))
+    kw = MATS[mat]
+    rp, ci, v = _rand_csr(rng, kw["h"], kw["w"], kw["avg"], kw["empty"], None, dtype)
+    h, w = kw["h"], kw["w"]
+    x, y0 = rng.random(w).astype(dtype), rng.random(h).astype(dtype)
+    alpha, beta = dtype(1.25), dtype(-0.75)
+    ref = oracle.spmv(rp, ci, v, x, y0.copy(), alpha, beta)
+    drp, dci, dv, dx = (_t(dev, a) for a in (rp, ci, v, x))
+    plan = K.Plan(drp, len(ci))
+    assert plan.build_colpanels(dci, dv, w) == (0, 0)          # automatic: x is tiny, no mirror
+    with pytest.raises(sblas.SblasError, match="COLPANEL"):
+        K.spmv(drp, dci, dv, dx, _t(dev, y0), alpha, beta, plan=plan, opts=sblas.make_opts(variant=sblas.SPMV_COLPANEL))
+    n, W = plan.build_colpanels(dci, dv, w, n_panels=panels)
+    assert n == panels and W % 32 == 0 and n * W >= w
+    bound = _row_bound(oracle, rp, ci, v, x, alpha, beta, y0)
+    for lanes in (0, 1, 8):
+        dy = _t(dev, y0)
+        rep = _t(dev, np.full(h, -3.0, dtype))
+        K.spmv(drp, dci, dv, dx, dy, alpha, beta, plan=plan,      # AUTO takes the mirror once the plan holds it
+               opts=sblas.make_opts(lanes=lanes, replicas=[rep.data_ptr()]))
+        torch.cuda.synchronize()
+        got = dy.cpu().numpy()
+        _check(got, ref, bound, dtype, exact=(lanes == 1))
+        assert np.array_equal(rep.cpu().numpy(), got)
+    # the plain kernel is still there on request, and agrees
+    dy = _t(dev, y0)
+    K.spmv(drp, dci, dv, dx, dy, alpha, beta, plan=plan, opts=sblas.make_opts(variant=sblas.SPMV_PIPE))
+    _check(dy.cpu().numpy(), ref, bound, dtype)
+
+
+@pytest.mark.gpu
+def test_spmv_column_panels_partials(sblas, dev, oracle):
+    """HEAD / TAIL partial rows of a multi-GPU segment go to the carry buffer from the LAST panel pass (raw sums)."""
+    import torch
+    K = sblas.kernels
+    rng = np.random.default_rng(4)
+    h, w = 700, 5000
+    rp, ci, v = _rand_csr(rng, h, w, 12, 0.0, None, np.float64)
+    x, y0 = rng.random(w), rng.random(h)
+    raw = oracle.spmv(rp, ci, v, x, np.zeros(h), 1.0, 0.0)
+    ref = oracle.spmv(rp, ci, v, x, y0.copy(), 2.0, 3.0)
+    drp, dci, dv, dx, dy = (_t(dev, a) for a in (rp, ci, v, x, y0))
+    carry = torch.full((8,), -1.0, dtype=torch.float64, device=dev)
+    plan = K.Plan(drp, len(ci))
+    plan.build_colpanels(dci, dv, w, n_panels=5)
+    K.spmv(drp, dci, dv, dx, dy, 2.0, 3.0, plan=plan,
+           opts=sblas.make_opts(lanes=1, flags=sblas.FLAG_HEAD_PARTIAL | sblas.FLAG_TAIL_PARTIAL, carry=carry.data_ptr()))
+    torch.cuda.synchronize()
+    y, c = dy.cpu().numpy(), carry.cpu().numpy()
+    assert np.array_equal(y[1:-1], ref[1:-1]) and y[0] == y0[0] and y[-1] == y0[-1]
+    assert c[0] == raw[0] and c[4] == raw[-1]
+
+
+@pytest.mark.gpu
+def test_spmv_column_panels_auto_on_gather_heavy(sblas, dev, oracle):
+    """Automatic build (what sync2gpu asks for): an x above 96 MB with uniform-random columns gets the mirror
+    (x slices of 32 MB), banded columns do not; AUTO then runs the panels and matches the oracle."""
+    import torch
+    K = sblas.kernels
+    rows, cols, deg = 20000, 14_000_000, 8
+    rng = np.random.default_rng(13)
+    rp = (np.arange(rows + 1, dtype=np.int64) * deg).astype(np.int32)
+    x, y0 = rng.random(cols), rng.random(rows)
+    for kind in ("random", "banded"):
+        if kind == "random":
+            ci = np.sort(rng.integers(0, cols, (rows, deg)), axis=1).astype(np.int32).reshape(-1)
+        else:
+            ci = (np.arange(rows)[:, None] * 3 + np.arange(deg)[None, :]).astype(np.int32).reshape(-1)
+        v = rng.standard_normal(rows * deg)
+        ref = oracle.spmv(rp, ci, v, x, y0.copy(), 1.5, -0.5)
+        drp, dci, dv, dx, dy = (_t(dev, a) for a in (rp, ci, v, x, y0))
+        plan = K.Plan(drp, len(ci)).prepare(dci, cols, 8)
+        assert (plan.col_jump() > cols / 256.0) == (kind == "random")
+        n, W = plan.build_colpanels(dci, dv, cols)
+        assert (n, W) == ((4, 3500000) if kind == "random" else (0, 0)), (kind, n, W)
+        K.spmv(drp, dci, dv, dx, dy, 1.5, -0.5, plan=plan, cols=cols)
+        torch.cuda.synchronize()
+        _check(dy.cpu().numpy(), ref, _row_bound(oracle, rp, ci, v, x, 1.5, -0.5, y0), np.float64)
+
+
+@pytest.mark.gpu
 def test_python_container_mirrors(sblas, oracle, golden):
     """The host mirror's CooSparseMatrix / CscSparseMatrix / CsrToCsc / CscToCsr (unit_test.cu:20-51)."""
     A = sblas.CsrSparseMatrix(golden["ash85_path"])
