@@ -199,13 +199,18 @@ SBLAS_API int sblas_plan_prepare_i32(void* stream, sblasPlan_t plan, const int32
  * gathering only from an L2-resident slice of x, the raw running row sums carried from pass to pass (rows whose
  * columns ascend are still summed in CSR order).  n_panels = 0: automatic — built only when x (cols elements)
  * exceeds 96 MB and the plan's col_jump statistic exceeds cols / 256 (uniform-random columns), with x slices
- * of 32 MB (environment SBLAS_COLPANEL_MB); n_panels >= 1 forces that many panels (<= 32).  The mirror holds a
+ * of at most 48 MB (environment SBLAS_COLPANEL_MB); n_panels >= 1 forces that many panels (<= 32).  The mirror holds a
  * COPY of col_idx / val: rebuild it after changing them. */
 SBLAS_API int sblas_plan_build_colpanels_f64(void* stream, sblasPlan_t plan, const int32_t* d_colidx,
                                              const double* d_val, int32_t cols, int32_t n_panels);
 SBLAS_API int sblas_plan_build_colpanels_f32(void* stream, sblasPlan_t plan, const int32_t* d_colidx,
                                              const float* d_val, int32_t cols, int32_t n_panels);
 SBLAS_API int sblas_plan_colpanel_stats(sblasPlan_t plan, int32_t* n_panels, int32_t* panel_cols);
+/* Storage of the panels: *is_sell = 1 when they are kept in sliced-ELL form (32-row slices stored column-major,
+ * rows sorted by length inside windows of 256 rows; taken when its padding stays below 25 %, environment
+ * SBLAS_COLPANEL_SELL=0 forbids it), 0 for CSR panels run by the staged kernel; *stored_entries = entries held
+ * including padding. */
+SBLAS_API int sblas_plan_colpanel_format(sblasPlan_t plan, int32_t* is_sell, int64_t* stored_entries);
 /* Row-block mirror of A for SpMM ("matrix.h device CSR layout", built inside
  * CsrSparseMatrix::sync2gpu next to the CSR arrays of matrix.h:376-387): R (= 4) consecutive rows
  * form a block row, every distinct column of a block row becomes one block {col, presence mask,

@@ -66,6 +66,17 @@ struct ColPanels {
   void* d_part = nullptr;        // [rows] raw running row sums carried from pass to pass
   std::vector<int64_t> nnz_off;  // [n + 1]
   std::vector<sblasPlan_st*> sub;  // per panel: row statistics + tile tables
+  // sliced-ELL form of the panels (SELL-32-sigma256, colpanel.cu): when present the CSR arrays above are
+  // released and the passes run on these
+  struct Sell {
+    int32_t n_slices = 0;
+    int64_t padded = 0;           // stored entries (32 x sum of slice widths)
+    int32_t* d_perm = nullptr;    // [n_slices * 32] row of every sorted position (-1: none)
+    int32_t* d_sptr = nullptr;    // [n_slices + 1] first entry of every slice
+    int32_t* d_col = nullptr;     // [padded] column, -1 = padding; entry u of sorted position q at sptr[q/32] + u*32 + q%32
+    void* d_val = nullptr;
+  };
+  std::vector<Sell> sell;
 };
 
 }  // namespace sblas
@@ -87,6 +98,7 @@ struct sblasPlan_st {
   // ~1 for banded / stencil inputs, ~cols/nnz_per_row for random ones.  Measured lazily by the first AUTO SpMV
   // whose x does not fit L2 (spmv.cu, col_jump_kernel).
   double col_jump = -1.0;
+  int32_t pipe_tile = 0;  // merge items per tile of the staged SpMV kernel for this plan (0 = the default rule)
 };
 
 namespace sblas {
@@ -119,6 +131,8 @@ void colpanels_free(sblasPlan_st* plan);
 // consecutive rows look at unrelated parts of it)
 bool measure_gather_heavy(cudaStream_t st, sblasPlan_st* plan, const int32_t* rp, const int32_t* ci, int32_t rows,
                           int32_t cols, size_t elem_size);
+constexpr int kSellC = 32;       // slice height = one warp
+constexpr int kSellSigma = 256;  // rows sorted by length inside windows of this many rows (one CTA)
 // spmv.cu: builds the tile table the PIPE kernel will ask for (so that no SpMV call has to)
 int prepare_pipe_table(cudaStream_t st, sblasPlan_st* plan, bool* pipe_ok);
 

@@ -338,6 +338,53 @@ __device__ __forceinline__ void consume_rows(const int32_t* __restrict__ s_col,
   }
 }
 
+// Short rows (the column-panel passes: ~8 nnz per row and panel), two phases on the staged tile.
+// Why: with one lane per row the 8-element row stride makes the shared-memory reads of a warp 8-way (col_idx)
+// and 16-way (8-byte values) bank conflicts; those wavefronts share the L1TEX data pipe with the x gathers
+// (32 wavefronts per warp gather: every lane another line), 56 wavefronts per 32 nnz in all, and the pipe is
+// what the pass is bound by.  Phase A is flat and balanced: thread t takes elements t, t + BLOCK, ... of the
+// tile (conflict-free reads, UA independent gathers in flight per thread), the products overwrite the staged
+// values.  Phase B: G consecutive lanes read the consecutive products of ONE row (conflict-free, shared-memory
+// latency only) and shuffle-reduce; lane 0 adds the carried sum.  ~44 wavefronts per 32 nnz.
+template <typename T, int G, int BLOCK, typename Sink>
+__device__ __forceinline__ void consume_rows_flat(const int32_t* __restrict__ s_col, T* __restrict__ s_val,
+                                                  const int32_t* __restrict__ s_rp, int32_t nrows,
+                                                  int32_t n0, int32_t n1, const T* __restrict__ x,
+                                                  const Sink& sink) {
+  constexpr int UA = 6;
+  const int tid = threadIdx.x;
+  const int n0a = n0 & ~3, lo = n0 - n0a, hi = n1 - n0a;
+  for (int j0 = lo + tid; j0 < hi; j0 += BLOCK * UA) {
+    T vv[UA], xx[UA];
+#pragma unroll
+    for (int u = 0; u < UA; ++u) {
+      const int j = j0 + u * BLOCK;
+      if (j < hi) {
+        vv[u] = s_val[j];
+        xx[u] = __ldg(x + s_col[j]);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < UA; ++u) {
+      const int j = j0 + u * BLOCK;
+      if (j < hi) s_val[j] = mul_rn(vv[u], xx[u]);
+    }
+  }
+  __syncthreads();
+  constexpr int RPI = BLOCK / G;
+  const int gl = tid & (G - 1), gi = tid / G;
+  for (int i0 = 0; i0 < nrows; i0 += RPI) {  // block-uniform trip count
+    const int i = i0 + gi;
+    const bool valid = i < nrows;
+    const int s = valid ? s_rp[i] - n0a : 0, e = valid ? s_rp[i + 1] - n0a : 0;
+    T sum = 0;
+    for (int j = s + gl; j < e; j += G) sum = add_rn(sum, s_val[j]);
+#pragma unroll
+    for (int m = G / 2; m > 0; m >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, m);
+    if (valid && gl == 0) sink.put(i, add_rn(sink.init(i), sum));
+  }
+}
+
 // A tile made of a few long row pieces (mean >= kPipeBlockModeAvg nnz): the whole CTA strides
 // over one row at a time, warp-shuffle + shared-memory reduction, one barrier per row.
 constexpr int kPipeBlockModeAvg = 128;
@@ -404,7 +451,7 @@ struct SplitArgs {  // only read by the SPLIT instantiation
 };
 
 // CONSEC: CTA c walks a run of CONSECUTIVE tiles instead of c, c + grid, ... (see the host side)
-template <typename T, int BLOCK, int NSTAGE, int G, bool SPLIT, bool CONSEC = false>
+template <typename T, int BLOCK, int NSTAGE, int G, bool SPLIT, bool CONSEC = false, bool FLAT = false>
 __global__ void __launch_bounds__(BLOCK)
 spmv_pipe_kernel(const int32_t* __restrict__ tile_row, const int32_t* __restrict__ tile_nnz,
                  int32_t n_tiles, const int32_t* __restrict__ rowptr,
@@ -535,10 +582,56 @@ spmv_pipe_kernel(const int32_t* __restrict__ tile_row, const int32_t* __restrict
     } else if (nrows > 0) {
       // rows straight from the staged tile: G lanes per row, U gathers in flight per lane
       const PipeSink<T> ps{sink, st.y, r0};
-      consume_rows<T, G, (G == 1 ? 8 : 4), BLOCK, false>(st.col, st.val, st.rp, nrows, n0 & ~3, 0, 0, x, ps);
+      if (FLAT)
+        consume_rows_flat<T, G, BLOCK>(st.col, st.val, st.rp, nrows, n0, n1, x, ps);
+      else
+        consume_rows<T, G, (G == 1 ? 8 : 4), BLOCK, false>(st.col, st.val, st.rp, nrows, n0 & ~3, 0, 0, x, ps);
     }
     fence_proxy_async_smem();  // my generic-proxy accesses of this stage precede its next bulk fill
     __syncthreads();
+  }
+}
+
+// ---- SELL: one pass over a column panel kept in sliced-ELL form (colpanel.cu) ---------------------------
+// One warp per slice of 32 sorted rows, one CTA per window of 256 rows (8 slices).  Lane l walks ITS row front
+// to back — entry u at sptr[slice] + u*32 + l, so the col_idx / val loads of a warp are single coalesced lines
+// (streamed past L1), U of them and U x gathers in flight per lane — and adds the products in the row's
+// storage order with separately rounded multiply and add, continuing from the sum carried over from the
+// previous panels: bit-identical to spmv.h:24-30 when the row's columns ascend.  No shared memory, no
+// barrier; the 256 KB of the SM stay L1 for the gathers in flight.  Padding entries carry col = -1.
+template <typename T, int U>
+__global__ void __launch_bounds__(kSellSigma)
+spmv_sell_kernel(int32_t n_slices, const int32_t* __restrict__ sptr, const int32_t* __restrict__ perm,
+                 const int32_t* __restrict__ col, const T* __restrict__ val, const T* __restrict__ x,
+                 RowSink<T> sink) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  constexpr int SPW = kSellSigma / kSellC;  // slices per window
+  for (int64_t sl = (int64_t)blockIdx.x * SPW + warp; sl < n_slices; sl += (int64_t)gridDim.x * SPW) {
+    const int32_t p0 = __ldg(sptr + sl), p1 = __ldg(sptr + sl + 1);
+    const int32_t r = __ldg(perm + sl * kSellC + lane);
+    T sum = (sink.phase >= 2 && r >= 0) ? sink.part[r] : T(0);
+    for (int32_t p = p0 + lane; p < p1; p += U * kSellC) {
+      int32_t c[U];
+      T v[U], xv[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        c[u] = -1;
+        if (p + u * kSellC < p1) {
+          c[u] = ldg_stream(col + p + u * kSellC);
+          v[u] = ldg_stream(val + p + u * kSellC);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        if (c[u] >= 0) xv[u] = __ldg(x + c[u]);
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        if (c[u] >= 0) sum = add_rn(sum, mul_rn(v[u], xv[u]));
+    }
+    if (r >= 0) {
+      if (sink.phase == 0) sink.put(r, sum);   // a single panel: plain fused epilogue (reads y[r] itself)
+      else sink.put_y(r, sum, T(0));           // phases 1-3 never use the staged value
+    }
   }
 }
 
@@ -898,6 +991,14 @@ static const void* pipe_kernel_ptr(int stages, int G) {
 #undef SBLAS_PK
 }
 
+// short-row flavour (consume_rows_flat): 2 stages, strided tile order; G = lanes per row of its reduction phase
+template <typename T>
+static const void* pipe_flat_kernel_ptr(int G) {
+#define SBLAS_PX(GG) (const void*)spmv_pipe_kernel<T, kSpmvBlock, 2, GG, false, false, true>
+  return G <= 2 ? SBLAS_PX(2) : G == 4 ? SBLAS_PX(4) : G == 8 ? SBLAS_PX(8) : G == 16 ? SBLAS_PX(16) : SBLAS_PX(32);
+#undef SBLAS_PX
+}
+
 // Column locality of consecutive rows, sampled: sum over ~4096 evenly spaced rows r (r and r+1 both non-empty)
 // of |colidx[rowptr[r+1]] - colidx[rowptr[r]]|, and the number of samples.
 __global__ void col_jump_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colidx,
@@ -970,6 +1071,7 @@ static int set_smem_once(const void* fn, int bytes) {
 
 // tile (merge items) PIPE uses for a plan: every row must fit a stage's staging buffer
 static int32_t pipe_tile_for(const sblasPlan_st* plan) {
+  if (plan->pipe_tile > 0) return plan->pipe_tile;
   return std::max<int32_t>(kSpmvPipeDefaultTile,
                            std::min<int32_t>(2 * kSpmvPipeMaxRow, (2 * plan->max_row_nnz + 511) & ~511));
 }
@@ -986,7 +1088,7 @@ int prepare_pipe_table(cudaStream_t st, sblasPlan_st* plan, bool* pipe_ok) {
 template <typename T>
 static int launch_pipe(cudaStream_t st, sblasPlan_st* plan, int32_t rows, int64_t nnz, const int32_t* rp,
                        const int32_t* ci, const T* v, const T* x, const RowSink<T>& sink, const sblasOpts* o,
-                       bool auto_gather, int* fallback) {
+                       bool auto_gather, int* fallback, bool short_rows = false) {
   *fallback = 0;
   if (!(aligned16(ci) && aligned16(v))) { *fallback = SBLAS_SPMV_TILE; return 0; }
   const int32_t tile = (o && o->tile > 0) ? o->tile : pipe_tile_for(plan);
@@ -1003,7 +1105,15 @@ static int launch_pipe(cudaStream_t st, sblasPlan_st* plan, int32_t rows, int64_
   const size_t smem = smem_for(stages);
   // lanes per row from the mean row length (one instantiation per launch keeps the
   // kernel small: ~50 registers instead of 160 with an in-kernel switch)
-  const int G = (o && o->lanes > 0) ? o->lanes : pow2_lanes_pipe(rows ? (double)(nnz / rows) : 0.0);  // integer mean, as the per-tile rule of TILE
+  int G = (o && o->lanes > 0) ? o->lanes : pow2_lanes_pipe(rows ? (double)(nnz / rows) : 0.0);  // integer mean, as the per-tile rule of TILE
+  // column-panel passes (short_rows): the two-phase flat consumer, its reduction phase with one lane group per
+  // row as wide as the mean row; opts->lanes = 1 keeps the one-lane-per-row kernel (the CPU loop's order)
+  const bool flat = short_rows && !(o && o->lanes == 1) && stages == 2;
+  if (flat && !(o && o->lanes > 1)) {
+    const double mean = rows ? (double)nnz / rows : 0.0;
+    G = 2;
+    while (G < 32 && G < mean) G <<= 1;
+  }
   // tile order: CTA c takes tiles c, c+grid, ... (the resident CTAs sweep one contiguous window of A and
   // share x through L2: best while x fits L2, c2 74 us against 86 us) or a run of consecutive tiles (the x
   // lines of neighbouring tiles stay in the CTA's own L1: best when x is larger than L2 and rows are local,
@@ -1015,7 +1125,8 @@ static int launch_pipe(cudaStream_t st, sblasPlan_st* plan, int32_t rows, int64_
   const bool big_window = plan->col_jump >= 0.0 && !auto_gather &&
                           plan->col_jump * (double)rows * sizeof(T) > (double)kGatherHeavyXBytes;
   const bool consec = env_consec >= 0 ? env_consec != 0 : big_window;
-  const void* kern = consec ? pipe_kernel_ptr<T, false, true>(stages, G) : pipe_kernel_ptr<T, false>(stages, G);
+  const void* kern = flat ? pipe_flat_kernel_ptr<T>(G)
+                          : consec ? pipe_kernel_ptr<T, false, true>(stages, G) : pipe_kernel_ptr<T, false>(stages, G);
   int per_sm = 0, n_sm = kNumSM;
   if ((rc = kernel_residency(kern, kSpmvBlock, smem, &per_sm, &n_sm)) != 0) return rc;
   const int grid = std::min<int>(tt->n_tiles, n_sm * per_sm);
@@ -1079,17 +1190,31 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
     // only from x[p*W, (p+1)*W), which stays L2-resident while the panel streams by
     const ColPanels& cp = plan->cp;
     sblasOpts po;
-    if (o) { po = *o; po.tile = 0; }
+    if (o) { po = *o; po.tile = 0; }   // the panels' tile tables were sized at build time
     for (int p = 0; p < cp.n && rc == 0; ++p) {
       RowSink<T> ps = sink;
       ps.part = (T*)cp.d_part;
       ps.phase = cp.n == 1 ? 0 : p == 0 ? 1 : p == cp.n - 1 ? 3 : 2;
       ps.stage_src = ps.phase == 0 ? y : ps.phase == 1 ? nullptr : (const T*)cp.d_part;
+      if (!cp.sell.empty()) {
+        // sliced-ELL panels: one CTA per window of 256 rows, persistent over the windows
+        const ColPanels::Sell& sl = cp.sell[(size_t)p];
+        const int n_win = sl.n_slices / (kSellSigma / kSellC);
+        const void* kern = (const void*)spmv_sell_kernel<T, 4>;
+        int per_sm = 0, n_sm = kNumSM;
+        if ((rc = kernel_residency(kern, kSellSigma, 0, &per_sm, &n_sm)) != 0) break;
+        const int grid = std::max(1, std::min(n_win, n_sm * per_sm));
+        spmv_sell_kernel<T, 4><<<grid, kSellSigma, 0, st>>>(sl.n_slices, sl.d_sptr, sl.d_perm, sl.d_col, (const T*)sl.d_val, x, ps);
+        ++g_launches;
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) { set_error("spmv sell launch: %s", cudaGetErrorString(e)); rc = 3; }
+        continue;
+      }
       sblasPlan_st* sub = cp.sub[(size_t)p];
       const int64_t off = cp.nnz_off[(size_t)p];
       int fb = 0;
       rc = launch_pipe<T>(st, sub, rows, sub->nnz, sub->d_rowptr, cp.d_colidx + off, (const T*)cp.d_val + off, x, ps,
-                          o ? &po : nullptr, false, &fb);
+                          o ? &po : nullptr, false, &fb, true);
       if (rc == 0 && fb != 0) { set_error("spmv: column panel %d cannot be staged by the PIPE kernel", p); rc = 5; }
     }
     return rc;

@@ -183,6 +183,12 @@ class Plan:
         check(lib().sblas_plan_colpanel_stats(self.handle, C.byref(n), C.byref(w)), "plan_colpanel_stats")
         return int(n.value), int(w.value)
 
+    def colpanel_format(self):
+        """(is_sell, stored_entries) of the column-panel mirror (sblas_plan_colpanel_format)."""
+        a, b = C.c_int32(), C.c_int64()
+        check(lib().sblas_plan_colpanel_format(self.handle, C.byref(a), C.byref(b)), "plan_colpanel_format")
+        return bool(a.value), int(b.value)
+
     def rowblock_stats(self):
         R, nb, fill = C.c_int32(), C.c_int64(), C.c_double()
         check(lib().sblas_plan_rowblock_stats(self.handle, C.byref(R), C.byref(nb), C.byref(fill)),

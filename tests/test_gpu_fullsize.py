@@ -69,10 +69,12 @@ def test_c4_full_size(sblas, dev, oracle):
 
 def test_c3v_full_size_column_panels(sblas, dev, oracle):
     """the north star's SpMV shape: uniform-random 16M x 32, fp64; x (134 MB) does not fit L2, sync2gpu builds the
-    column-panel mirror (4 panels of 32 MB of x) and AUTO runs it; nnz offsets reach 2^29."""
+    column-panel mirror (3 panels of 43 MB of x, sliced-ELL) and AUTO runs it; nnz offsets reach 2^29."""
     def expect(plan, panels):
         assert plan.col_jump() > (1 << 24) / 256.0
-        assert panels[0] == 4 and panels[1] == (1 << 22), panels
+        assert panels == (3, 5592416), panels
+        is_sell, stored = plan.colpanel_format()
+        assert is_sell and stored <= 1.25 * (1 << 29)
     _spmv_case(sblas, dev, oracle, lambda td: sblas.synth.uniform(1 << 24, 1 << 24, 32, td, dev), "f64", 4096, expect)
 
 

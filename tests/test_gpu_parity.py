@@ -644,7 +644,8 @@ def test_spmv_auto_gather_heavy(sblas, dev, oracle):
 @pytest.mark.parametrize("dtype", [np.float64, np.float32])
 @pytest.mark.parametrize("mat", ["short", "mid", "long", "empty_tail", "tiny"])
 @pytest.mark.parametrize("panels", [1, 2, 3, 7, 32])
-def test_spmv_column_panels(sblas, dev, oracle, dtype, mat, panels):
+@pytest.mark.parametrize("fmt", ["sell", "csr"])
+def test_spmv_column_panels(sblas, dev, oracle, dtype, mat, panels, fmt, monkeypatch):
     """SBLAS_SPMV_COLPANEL (colpanel.cu): one PIPE pass per column panel, the raw running row sums carried from
     pass to pass.  Within the row tolerance for every shape; with one lane per row (lanes = 1) and ascending
     columns the accumulation order is the CPU loop's, so the result is bit-identical to spmv.h:24-30."""
@@ -659,11 +660,18 @@ def test_spmv_column_panels(sblas, dev, oracle, dtype, mat, panels):
     ref = oracle.spmv(rp, ci, v, x, y0.copy(), alpha, beta)
     drp, dci, dv, dx = (_t(dev, a) for a in (rp, ci, v, x))
     plan = K.Plan(drp, len(ci))
+    # panels kept as sliced-ELL (32-row slices, rows sorted by length in windows of 256; taken when padding stays
+    # below 25 %) or as CSR panels run by the staged kernel
+    monkeypatch.setenv("SBLAS_COLPANEL_SELL", "1" if fmt == "sell" else "0")
     assert plan.build_colpanels(dci, dv, w) == (0, 0)          # automatic: x is tiny, no mirror
     with pytest.raises(sblas.SblasError, match="COLPANEL"):
         K.spmv(drp, dci, dv, dx, _t(dev, y0), alpha, beta, plan=plan, opts=sblas.make_opts(variant=sblas.SPMV_COLPANEL))
     n, W = plan.build_colpanels(dci, dv, w, n_panels=panels)
     assert n == panels and W % 32 == 0 and n * W >= w
+    is_sell, stored = plan.colpanel_format()
+    assert stored >= len(ci) and (fmt == "sell" or not is_sell)
+    if is_sell:
+        assert stored * 4 <= len(ci) * 5 + h
     bound = _row_bound(oracle, rp, ci, v, x, alpha, beta, y0)
     for lanes in (0, 1, 8):
         dy = _t(dev, y0)
@@ -672,12 +680,37 @@ def test_spmv_column_panels(sblas, dev, oracle, dtype, mat, panels):
                opts=sblas.make_opts(lanes=lanes, replicas=[rep.data_ptr()]))
         torch.cuda.synchronize()
         got = dy.cpu().numpy()
-        _check(got, ref, bound, dtype, exact=(lanes == 1))
+        _check(got, ref, bound, dtype, exact=(lanes == 1 or is_sell))   # one lane per row walks it in CSR order
         assert np.array_equal(rep.cpu().numpy(), got)
     # the plain kernel is still there on request, and agrees
     dy = _t(dev, y0)
     K.spmv(drp, dci, dv, dx, dy, alpha, beta, plan=plan, opts=sblas.make_opts(variant=sblas.SPMV_PIPE))
     _check(dy.cpu().numpy(), ref, bound, dtype)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_spmv_column_panels_sliced_ell(sblas, dev, oracle, dtype, monkeypatch):
+    """Even row lengths (the shape the mirror is built for): the panels are kept in sliced-ELL form, the result
+    is bit-identical to the CPU loop (every lane walks its row in storage order), rows % 256 != 0."""
+    import torch
+    K = sblas.kernels
+    monkeypatch.setenv("SBLAS_COLPANEL_SELL", "1")
+    rng = np.random.default_rng(21)
+    h, w, deg = 5000 + 77, 60000, 32
+    rp = (np.arange(h + 1, dtype=np.int64) * deg).astype(np.int32)
+    ci = np.sort(rng.integers(0, w, (h, deg)), axis=1).astype(np.int32).reshape(-1)
+    v = (rng.random(h * deg) * 2 - 1).astype(dtype)
+    x, y0 = rng.random(w).astype(dtype), rng.random(h).astype(dtype)
+    ref = oracle.spmv(rp, ci, v, x, y0.copy(), dtype(0.5), dtype(2.0))
+    drp, dci, dv, dx, dy = (_t(dev, a) for a in (rp, ci, v, x, y0))
+    plan = K.Plan(drp, len(ci))
+    assert plan.build_colpanels(dci, dv, w, n_panels=4)[0] == 4
+    is_sell, stored = plan.colpanel_format()
+    assert is_sell and len(ci) <= stored <= 1.25 * len(ci) + h
+    K.spmv(drp, dci, dv, dx, dy, 0.5, 2.0, plan=plan)
+    torch.cuda.synchronize()
+    assert np.array_equal(dy.cpu().numpy(), ref)
 
 
 @pytest.mark.gpu
@@ -706,7 +739,7 @@ def test_spmv_column_panels_partials(sblas, dev, oracle):
 @pytest.mark.gpu
 def test_spmv_column_panels_auto_on_gather_heavy(sblas, dev, oracle):
     """Automatic build (what sync2gpu asks for): an x above 96 MB with uniform-random columns gets the mirror
-    (x slices of 32 MB), banded columns do not; AUTO then runs the panels and matches the oracle."""
+    (x slices of at most 48 MB), banded columns do not; AUTO then runs the panels and matches the oracle."""
     import torch
     K = sblas.kernels
     rows, cols, deg = 20000, 14_000_000, 8
@@ -724,7 +757,7 @@ def test_spmv_column_panels_auto_on_gather_heavy(sblas, dev, oracle):
         plan = K.Plan(drp, len(ci)).prepare(dci, cols, 8)
         assert (plan.col_jump() > cols / 256.0) == (kind == "random")
         n, W = plan.build_colpanels(dci, dv, cols)
-        assert (n, W) == ((4, 3500000) if kind == "random" else (0, 0)), (kind, n, W)
+        assert (n, W) == ((3, 4666688) if kind == "random" else (0, 0)), (kind, n, W)
         K.spmv(drp, dci, dv, dx, dy, 1.5, -0.5, plan=plan, cols=cols)
         torch.cuda.synchronize()
         _check(dy.cpu().numpy(), ref, _row_bound(oracle, rp, ci, v, x, 1.5, -0.5, y0), np.float64)

@@ -51,9 +51,13 @@ def main():
         print(json.dumps(dict(kernel=name, ms=ms, frac=ab / ms / 1e6 / peak)), flush=True)
     yref = torch.ones(rows, dtype=td, device=dev)
     K.spmv(rp, ci, v, x, yref, 1.0, 1.0, plan=plan, opts=pkg.make_opts(variant=pkg.SPMV_PIPE), cols=cols)
-    for P in [int(a) for a in (sys.argv[2].split(",") if len(sys.argv) > 2 else "2,3,4,6,8,12,16".split(","))]:
+    tiles = [int(a) for a in (sys.argv[3].split(",") if len(sys.argv) > 3 else ["0"])]
+    for P, tile in [(int(a), t) for a in (sys.argv[2].split(",") if len(sys.argv) > 2 else "2,3,4,6,8,12,16".split(",")) for t in tiles]:
+        if tile:
+            os.environ["SBLAS_COLPANEL_TILE"] = str(tile)
         n, W = plan.build_colpanels(ci, v, cols, n_panels=P)
-        for lanes in (0, 1, 2, 4, 8):
+        print("tile", tile, "format(is_sell, stored)", plan.colpanel_format(), "nnz", nnz, flush=True)
+        for lanes in (0, 1, 4, 8, 16):
             o = pkg.make_opts(lanes=lanes)
             ms = timeit(lambda: K.spmv(rp, ci, v, x, y, 1.0, 1.0, plan=plan, opts=o, cols=cols))
             y2 = torch.ones(rows, dtype=td, device=dev)

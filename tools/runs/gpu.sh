@@ -26,8 +26,8 @@ for step in "$@"; do
   case "$kind" in
     tests)
       run "$step"
-      timeout 2400 python -m pytest tests -m gpu -q -x --timeout=600 -p no:cacheprovider ${a:+-k "$a"} > gpurun_out/pytest_gpu.log 2>&1
-      echo "pytest exit $?"; tail -5 gpurun_out/pytest_gpu.log ;;
+      timeout 2400 python -m pytest tests -m gpu -q -rf --timeout=600 -p no:cacheprovider ${a:+-k "$a"} > gpurun_out/pytest_gpu.log 2>&1
+      echo "pytest exit $?"; grep -E "^(FAILED|ERROR)" gpurun_out/pytest_gpu.log | cut -c1-300 | head -40; tail -3 gpurun_out/pytest_gpu.log ;;
     smoke)
       run "$step"
       timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke exit $?"; tail -2 gpurun_out/smoke.log ;;
