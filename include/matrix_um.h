@@ -76,6 +76,19 @@ class CsrSparseMatrix {
     free(tmp);
     printf("input matrix A: ( %i, %i ) nnz = %i\n", m, n, nnzA);
   }
+  /* Not in the reference: adopt host arrays (copied into managed memory), for synthetic matrices. */
+  CsrSparseMatrix(IdxType h, IdxType w, const IdxType* rowptr, const IdxType* colidx, const DataType* val) {
+    clear_();
+    height = h;
+    width = w;
+    nnz = rowptr[h];
+    SAFE_ALOC_MANAGED(csrRowPtr, get_row_ptr_size());
+    SAFE_ALOC_MANAGED(csrColIdx, get_col_idx_size());
+    SAFE_ALOC_MANAGED(csrVal, get_val_size());
+    memcpy(csrRowPtr, rowptr, get_row_ptr_size());
+    memcpy(csrColIdx, colidx, get_col_idx_size());
+    memcpy(csrVal, val, get_val_size());
+  }
   ~CsrSparseMatrix() {
     release_gpu_();
     SAFE_FREE_MANAGED(csrRowPtr);

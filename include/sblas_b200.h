@@ -76,6 +76,9 @@ enum {
                                   (which stays within the north star's 1e-12 / 1e-5 relative row tolerance and
                                   halves the FP64 instruction count).  SBLAS_EXACT=1 in the environment or
                                   sblas_set_spmm_exact(1) make it the default; SBLAS_FLAG_FMA then opts out */
+  SBLAS_FLAG_STITCH_DIRECT = 2048, /* replicas (sblasOpts.replica) are written by the computing lanes' own st.global
+                                  instead of TMA bulk stores of staged row chunks (the default for wide SpMM rows):
+                                  needed for NVSwitch multicast addresses, kept as the comparison point */
   SBLAS_FLAG_HEAD_PARTIAL = 2, /* local row 0 continues a row begun on the previous GPU
                                   (matrix.h:443-445): its sum goes to carry[0..k), not to y/C */
   SBLAS_FLAG_TAIL_PARTIAL = 4, /* local last row continues on the next GPU: sum -> carry[k..2k) */

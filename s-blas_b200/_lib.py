@@ -19,6 +19,7 @@ FLAG_SPLIT_SERIAL = 128
 FLAG_SPLIT_SEG = 256
 FLAG_PREFETCH_C = 512
 FLAG_EXACT = 1024
+FLAG_STITCH_DIRECT = 2048
 ROW_MAJOR, COL_MAJOR = 0, 1
 
 

@@ -119,12 +119,19 @@ __device__ __forceinline__ void emit_row_slice(const MatSink<T>& sink, int64_t o
 // ---- ROWMAJOR ---------------------------------------------------------------------------------
 // G lanes per A row, VEC elements per lane per column block, NB column blocks per lane:
 // covers k <= G*VEC*NB columns (larger k: the host loops over column panels).
-template <typename T, int VEC, int G, int NB, bool EXACT, int BLOCK>
+// BULK (the stitch of method 2 / SpMV v1 for wide rows): the finished rows of a chunk of the tile are also parked
+// in shared memory — consecutive rows, so with ldc == k one contiguous block of C — and pushed to every peer
+// replica by TMA bulk stores (cp.async.bulk.global.shared::cta, SASS UBLKCP: one instruction per peer and chunk,
+// 16-32 KB each) instead of seven 16-byte st.global per lane: the LSU of the computing warps carries no NVLink
+// traffic, the copies drain while the CTA's other rows (and the SM's other CTAs) compute.  chunk_rows (a
+// multiple of GPB) rows fit the dynamic shared memory; rows that go to the carry buffer are left out.
+template <typename T, int VEC, int G, int NB, bool EXACT, int BLOCK, bool BULK = false>
 __global__ void __launch_bounds__(BLOCK)
 spmm_rm_kernel(const int32_t* __restrict__ tile_row, const int32_t* __restrict__ rowptr,
                const int32_t* __restrict__ colidx, const T* __restrict__ val,
-               const T* __restrict__ B, int64_t ldb, MatSink<T> sink) {
+               const T* __restrict__ B, int64_t ldb, MatSink<T> sink, int32_t chunk_rows) {
   using V = typename VecT<T, VEC>::type;
+  extern __shared__ __align__(128) unsigned char rm_stage[];
   constexpr int GPB = BLOCK / G;  // row groups per CTA
   constexpr int U = NB >= 8 ? 1 : NB >= 4 ? 2 : 4;  // nnz per step (MLP = U*NB gathers per lane)
   const int lane = threadIdx.x & 31;
@@ -132,10 +139,14 @@ spmm_rm_kernel(const int32_t* __restrict__ tile_row, const int32_t* __restrict__
   const int gi = threadIdx.x / G;
   const int32_t r0 = tile_row[blockIdx.x], r1 = tile_row[blockIdx.x + 1];
   const int k = sink.k;
+  const uint32_t rowbytes = (uint32_t)k * (uint32_t)sizeof(T);
+  if (!BULK) chunk_rows = r1 - r0 > 0 ? r1 - r0 : 1;
 
-  for (int32_t rb = r0; rb < r1; rb += GPB) {  // block-uniform
+ for (int32_t cr0 = r0; cr0 < r1; cr0 += chunk_rows) {  // block-uniform
+  const int32_t cr1 = min(cr0 + chunk_rows, r1);
+  for (int32_t rb = cr0; rb < cr1; rb += GPB) {  // block-uniform
     const int32_t r = rb + gi;
-    const bool valid = r < r1;
+    const bool valid = r < cr1;
     const int32_t s = valid ? rowptr[r] : 0;
     const int32_t len = valid ? rowptr[r + 1] - s : 0;
     const int32_t maxlen = (G == 32) ? len : warp_max(len);
@@ -196,6 +207,11 @@ spmm_rm_kernel(const int32_t* __restrict__ tile_row, const int32_t* __restrict__
         if (c0 < k) {
           if (slot >= 0) {
             *reinterpret_cast<V*>(sink.carry + (int64_t)slot * sink.kpad + c0) = acc[nb];
+          } else if (BULK) {   // full vectors only (host: k % VEC == 0)
+            const int64_t off = (int64_t)r * sink.ldc + c0;
+            const V res = vaxpby(sink.alpha, acc[nb], sink.beta, *reinterpret_cast<const V*>(sink.C + off));
+            *reinterpret_cast<V*>(sink.C + off) = res;
+            *reinterpret_cast<V*>(rm_stage + (size_t)(r - cr0) * rowbytes + (size_t)c0 * sizeof(T)) = res;
           } else {
             emit_row_slice<T, VEC>(sink, (int64_t)r * sink.ldc + c0, c0, acc[nb]);
           }
@@ -203,6 +219,31 @@ spmm_rm_kernel(const int32_t* __restrict__ tile_row, const int32_t* __restrict__
       }
     }
   }
+  if (BULK) {
+    fence_proxy_async_smem();   // my generic-proxy writes of the staged rows precede the bulk reads
+    __syncthreads();
+    // rows of the chunk that belong in the replicas: all but a HEAD / TAIL partial row (those travel as carries)
+    int32_t a = cr0, b = cr1;
+    if ((sink.flags & SBLAS_FLAG_HEAD_PARTIAL) && a == 0) ++a;
+    if ((sink.flags & SBLAS_FLAG_TAIL_PARTIAL) && b == sink.rows) --b;
+    if (sink.ldc == k) {      // the rows are one contiguous block of C
+      if (threadIdx.x == 0 && b > a) {
+        for (int d = 0; d < sink.out.n; ++d)
+          bulk_s2g(sink.out.ptr[d] + (int64_t)a * sink.ldc, rm_stage + (size_t)(a - cr0) * rowbytes, (uint32_t)(b - a) * rowbytes);
+        bulk_commit();
+        bulk_wait_read_all();
+      }
+    } else if ((int)threadIdx.x < b - a) {   // pitched C: one bulk store per row and peer
+      const int32_t row = a + (int)threadIdx.x;
+      for (int d = 0; d < sink.out.n; ++d)
+        bulk_s2g(sink.out.ptr[d] + (int64_t)row * sink.ldc, rm_stage + (size_t)(row - cr0) * rowbytes, rowbytes);
+      bulk_commit();
+      bulk_wait_read_all();
+    }
+    if (cr1 < r1) __syncthreads();   // the stage is free for the next chunk
+  }
+ }
+  if (BULK) bulk_wait_all();   // the peers hold my rows before the CTA retires (the stream's next kernel signals them)
 }
 
 // ---- ROWBLOCK (row-major B/C, R x 1 BCSR mirror of A, spmm_rb.cu) --------------------------------
@@ -990,9 +1031,33 @@ template <typename T, int VEC, bool EXACT>
 static int launch_rm(cudaStream_t st, const TileTable* tt, int G, int NB, const int32_t* rp,
                      const int32_t* ci, const T* v, const T* B, int64_t ldb,
                      const MatSink<T>& sink) {
+  // the stitch by TMA bulk stores: wide rows (one warp per row), whole vectors, 16-byte row pitch; the flag
+  // SBLAS_FLAG_STITCH_DIRECT (multicast replicas, comparisons) and SBLAS_STITCH_BULK=0 keep the per-lane stores
+  static const int env_bulk = [] { const char* e = getenv("SBLAS_STITCH_BULK"); return e ? atoi(e) : 1; }();
+  if (VEC > 1 && G == 32 && sink.out.n > 0 && env_bulk && !(sink.flags & SBLAS_FLAG_STITCH_DIRECT) &&
+      sink.k % VEC == 0 && (sink.ldc * (int64_t)sizeof(T)) % 16 == 0) {
+    constexpr int GPB = kSpmmBlock / 32;
+    const size_t rowbytes = (size_t)sink.k * sizeof(T);
+    int32_t chunk = (int32_t)((32 * 1024) / rowbytes) / GPB * GPB;
+    chunk = std::max(chunk, GPB);
+    const size_t smem = (size_t)chunk * rowbytes;
+#define SBLAS_RMB(NN)                                                                                       \
+    {                                                                                                       \
+      auto kern = spmm_rm_kernel<T, VEC, 32, NN, EXACT, kSpmmBlock, true>;                                  \
+      if (smem > 48 * 1024) SBLAS_CUDA(cudaFuncSetAttribute((const void*)kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+      kern<<<tt->n_tiles, kSpmmBlock, smem, st>>>(tt->d_tile_row, rp, ci, v, B, ldb, sink, chunk);          \
+    }
+    if (NB == 1) SBLAS_RMB(1)
+    else if (NB == 2) SBLAS_RMB(2)
+    else if (NB <= 4) SBLAS_RMB(4)
+    else SBLAS_RMB(8)
+#undef SBLAS_RMB
+    SBLAS_LAUNCH_CHECK();
+    return 0;
+  }
 #define SBLAS_RM(GG, NN)                                                                         \
   spmm_rm_kernel<T, VEC, GG, NN, EXACT, kSpmmBlock>                                              \
-      <<<tt->n_tiles, kSpmmBlock, 0, st>>>(tt->d_tile_row, rp, ci, v, B, ldb, sink)
+      <<<tt->n_tiles, kSpmmBlock, 0, st>>>(tt->d_tile_row, rp, ci, v, B, ldb, sink, 0)
   if (G == 1) SBLAS_RM(1, 1);
   else if (G == 2) SBLAS_RM(2, 1);
   else if (G == 4) SBLAS_RM(4, 1);

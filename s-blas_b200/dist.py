@@ -153,7 +153,8 @@ class RowSplitOp:
             # into every rank's buffer (this rank's included), so a GPU sends |panel| bytes, not (n-1)x
             if not mc_ptr:
                 raise RuntimeError("stitch='mc' needs a multicast address (SymmBuffer.mc_ptr is 0 on this box)")
-            self.opts = make_opts(replicas=[mc_ptr + self.r0 * ld * val.element_size()], flags=flags)
+            from ._lib import FLAG_STITCH_DIRECT   # multicast addresses take plain stores, not TMA bulk copies
+            self.opts = make_opts(replicas=[mc_ptr + self.r0 * ld * val.element_size()], flags=flags | FLAG_STITCH_DIRECT)
             self.stitch = "peer"            # same device-side barrier closes the step
             peer_ptrs = None
         elif self.stitch == "peer":

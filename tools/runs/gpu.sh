@@ -10,7 +10,7 @@
 #   ncu:WL:REGEX[:ARGS]  ncu --set full of kernels matching REGEX              -> ncu_WL.ncu-rep (+ summary txt)
 #   sweep:WL[:ARGS]      tools/sweep.py                                        -> sweep_WL.log
 #   dist:N               tools/check_dist.py under torchrun                    -> check_dist_nN.log
-#   multi                tests/test_gpu_multi.py test_dropin.py test_gpu_dist.py with the identity device map
+#   multi                tests/test_gpu_multi.py test_dropin.py test_gpu_dist.py on all the devices of the box
 #   drv:ARGS             drivers/bin/bench_dropin ARGS                         -> dropin.log (appended)
 #   um                   managed-memory drivers, tuning 0 / 1                  -> um.log
 #   py:FILE[:ARGS]       python FILE ARGS                                      -> py_<basename>.log
@@ -73,9 +73,10 @@ for step in "$@"; do
       echo "check_dist $a exit $?"; tail -12 gpurun_out/check_dist_n$a.log ;;
     multi)
       run "$step"
-      SBLAS_DEVICE_MAP=0,1,2,3,4,5,6,7,8,9,10,11,12,13,14,15 timeout 1800 python -m pytest tests/test_gpu_multi.py tests/test_dropin.py tests/test_gpu_dist.py \
-        -m gpu -q --timeout=900 -p no:cacheprovider -rs > gpurun_out/pytest_multi_identity_map.log 2>&1
-      echo "multi exit $?"; tail -8 gpurun_out/pytest_multi_identity_map.log ;;
+      # tests/conftest.py maps logical GPU i to device i % (devices present): the identity on an 8-GPU box
+      timeout 1800 python -m pytest tests/test_gpu_multi.py tests/test_dropin.py tests/test_gpu_dist.py \
+        -m gpu -q --timeout=900 -p no:cacheprovider -rs > gpurun_out/pytest_multi_devices.log 2>&1
+      echo "multi exit $?"; tail -8 gpurun_out/pytest_multi_devices.log ;;
     drv)
       run "$step"
       timeout 900 drivers/bin/bench_dropin $a $b $c >> gpurun_out/dropin.log 2>&1; echo "drv exit $?"; tail -12 gpurun_out/dropin.log ;;
