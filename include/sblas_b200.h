@@ -241,6 +241,21 @@ SBLAS_API int sblas_spmv_csr_f32(void* stream, int32_t rows, int32_t cols, int64
                                  const float* d_val, const float* d_x, float* d_y, float alpha,
                                  float beta, sblasPlan_t plan, const sblasOpts* opts);
 
+/* y <- beta*y + alpha*A*x on the current device WITHOUT ANY ALLOCATION.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same result contract as sblas_spmv_csr_f64 (the merge-path SPLIT
+ * kernels: rows of any length, reduction order differs from the CPU loop within the 1e-12 row tolerance); its
+ * scratch (split table + per-tile carries) lives in a fixed 3.25 MiB device array inside the library, so
+ *   - rows + nnz must not exceed 201 326 592 (131 072 tiles of 1536 merge items) — larger inputs are rejected
+ *     with a clear error and nothing is launched;
+ *   - the call makes no cudaMalloc / cudaFree / allocating library call, takes no plan and synchronises nothing
+ *     (three kernel launches on `stream`);
+ *   - every call on a device shares the array: calls that OVERLAP on the GPU (different streams or host threads)
+ *     race — serialise them; nothing needs clearing between calls (each word read was written in the same call). */
+SBLAS_API int sblas_spmv_csr_noalloc_f64(void* stream, int32_t rows, int32_t cols, int64_t nnz,
+                                         const int32_t* d_rowptr, const int32_t* d_colidx, const double* d_val,
+                                         const double* d_x, double* d_y, double alpha, double beta);
+
 /* C <- beta*C + alpha*A*B on the current device, k dense columns.  Replaces cusparseSpMM
  * at spmm.h:135-149 (method 1) / :240-251 (method 2) plus the axpby of spmm.h:283.
  * layout = SBLAS_ROW_MAJOR: B[c*ldb + n], C[r*ldc + n] (the internal device layout);

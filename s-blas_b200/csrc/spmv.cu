@@ -17,6 +17,8 @@
 //  VECTOR classic sub-warp-per-row kernel straight from global memory; needs no plan.
 //  SPLIT  merge-path tiles in nnz space that cut long rows; partial sums of cut rows go
 //         to a carry array and the last CTA to finish folds them in (skewed inputs: R-MAT).
+#include <mutex>
+
 #include "plan.cuh"
 
 namespace sblas {
@@ -1408,3 +1410,88 @@ int sblas_plan_stats(sblasPlan_t p, sblasCsrStats* out) {
 }
 
 }  // extern "C"
+
+// ---- allocation-free SpMV (no counterpart in the reference) ------
+// For callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it):
+// the SPLIT kernels above (merge-path tiles that cut long rows + carry fix-up) with their scratch — the split
+// table and the per-tile carry / head arrays — in a file-scope device array of fixed size instead of plan-owned
+// cudaMalloc'ed buffers.  Every GPU that loads the library holds the array (3.25 MiB) until exit.  Every call shares
+// it and it keeps the last call's contents: each word a call reads was written earlier in the same call (the
+// split table by split_search_kernel, carry_out / head_row by every tile, head_val where head_row says so), so
+// nothing has to start at zero — but two calls that overlap on the GPU (different streams, or different host
+// threads) race on it.
+namespace sblas {
+constexpr int32_t kNoAllocTile = kSpmvSplitDefaultTile;                    // 1536 merge items per tile
+constexpr int64_t kNoAllocMaxTiles = 131072;                               // rows + nnz <= 201 326 592
+constexpr size_t kNoAllocScratchBytes = (3u << 20) + (256u << 10);          // 3.25 MiB: 4 + 8 + 8 + 4 B per tile, + slack
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocScratchBytes];
+static_assert((kNoAllocMaxTiles + 1) * 4 + 256 + kNoAllocMaxTiles * (8 + 8 + 4) + 256 <= (int64_t)kNoAllocScratchBytes,
+              "scratch layout does not fit");
+
+// the array's DEVICE address on the current device (the name itself is only a host-side stand-in): looked up
+// once per device, with that device current
+static int noalloc_scratch_ptr(unsigned char** out) {
+  static std::mutex mu;
+  static unsigned char* ptr[64] = {nullptr};
+  int dev = 0;
+  SBLAS_CUDA(cudaGetDevice(&dev));
+  SBLAS_CHECK(dev >= 0 && dev < 64, "spmv noalloc: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptr[dev]) {
+    unsigned char* p = nullptr;
+    SBLAS_CUDA(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
+    SBLAS_CHECK(p != nullptr, "spmv noalloc: cudaGetSymbolAddress returned a null address");
+    ptr[dev] = p;
+  }
+  *out = ptr[dev];
+  return 0;
+}
+}  // namespace sblas
+
+extern "C" int sblas_spmv_csr_noalloc_f64(void* stream, int32_t rows, int32_t cols, int64_t nnz, const int32_t* rp,
+                                          const int32_t* ci, const double* v, const double* x, double* y,
+                                          double alpha, double beta) {
+  using T = double;
+  cudaStream_t st = (cudaStream_t)stream;
+  SBLAS_CHECK(rows >= 0 && cols >= 0 && nnz >= 0 && nnz < (1ll << 31), "spmv noalloc: bad sizes");
+  if (rows == 0) return 0;
+  SBLAS_CHECK(rp && y && (nnz == 0 || (ci && v && x)), "spmv noalloc: null pointer");
+  const int32_t tile = kNoAllocTile;
+  const int64_t n_tiles64 = ceil_div(std::max<int64_t>((int64_t)rows + nnz, 1), tile);
+  SBLAS_CHECK(n_tiles64 <= kNoAllocMaxTiles,
+              "spmv noalloc: rows + nnz = %lld exceeds the fixed scratch (at most %lld; use sblas_spmv_csr_f64 with a plan)",
+              (long long)((int64_t)rows + nnz), (long long)(kNoAllocMaxTiles * tile));
+  const int32_t n_tiles = (int32_t)n_tiles64;
+  unsigned char* base = nullptr;
+  if (int rc = noalloc_scratch_ptr(&base)) return rc;
+  int32_t* split_row = reinterpret_cast<int32_t*>(base);
+  size_t off = (((size_t)kNoAllocMaxTiles + 1) * 4 + 255) & ~(size_t)255;
+  T* carry_out = reinterpret_cast<T*>(base + off);
+  T* head_val = carry_out + kNoAllocMaxTiles;
+  int32_t* head_row = reinterpret_cast<int32_t*>(head_val + kNoAllocMaxTiles);
+  RowSink<T> sink;
+  sink.y = y;
+  sink.out = make_outspec<T>(nullptr);
+  sink.carry = nullptr;
+  sink.rows = rows;
+  sink.flags = 0;
+  sink.alpha = alpha;
+  sink.beta = beta;
+  sink.part = nullptr;
+  sink.stage_src = y;
+  sink.phase = 0;
+  split_search_kernel<<<(int)ceil_div(n_tiles + 1, 256), 256, 0, st>>>(rp, rows, nnz, tile, n_tiles, split_row);
+  SBLAS_LAUNCH_CHECK();
+  const int32_t cap = (tile + 9) & ~3;
+  const int smem = cap * (int)sizeof(T) + (tile + 3) * (int)sizeof(int32_t) + ((tile + 31) / 32 + 2) * 4;  // < 48 KB: no attribute call
+  if (aligned16(ci) && aligned16(v))
+    spmv_split_kernel<T, kSpmvBlock, true, true><<<n_tiles, kSpmvBlock, smem, st>>>(split_row, tile, rows, nnz, rp, ci, v, x, sink,
+                                                                                   carry_out, head_val, head_row, cap);
+  else
+    spmv_split_kernel<T, kSpmvBlock, false, true><<<n_tiles, kSpmvBlock, smem, st>>>(split_row, tile, rows, nnz, rp, ci, v, x, sink,
+                                                                                    carry_out, head_val, head_row, cap);
+  SBLAS_LAUNCH_CHECK();
+  spmv_split_fixup_kernel<T><<<(int)ceil_div(n_tiles, 256), 256, 0, st>>>(rp, tile, n_tiles, carry_out, head_val, head_row, sink);
+  SBLAS_LAUNCH_CHECK();
+  return 0;
+}

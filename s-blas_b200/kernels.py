@@ -231,6 +231,17 @@ def spmv(rowptr, colidx, val, x, y, alpha, beta, plan=None, opts=None, cols=None
     return y
 
 
+def spmv_noalloc(rowptr, colidx, val, x, y, alpha, beta, cols=None, stream=None):
+    """sblas_spmv_csr_noalloc_f64: y <- beta*y + alpha*A*x with the scratch in a fixed device array of the library
+    (no cudaMalloc, no plan); fp64, rows + nnz <= 201 326 592; overlapping calls race on the scratch."""
+    rows, nnz = rowptr.numel() - 1, val.numel()
+    cols = x.numel() if cols is None else cols
+    check(lib().sblas_spmv_csr_noalloc_f64(stream_ptr(stream), C.c_int32(rows), C.c_int32(cols), C.c_int64(nnz),
+                                           vp(rowptr), vp(colidx), vp(val), vp(x), vp(y), C.c_double(float(alpha)),
+                                           C.c_double(float(beta))), "spmv_noalloc")
+    return y
+
+
 def spmm(rowptr, colidx, val, k, layout, B, ldb, Cm, ldc, alpha, beta, cols, plan=None, opts=None,
          stream=None):
     """C <- beta*C + alpha*A*B (spmm.h:55-68 semantics); layout ROW_MAJOR / COL_MAJOR."""
