@@ -268,6 +268,7 @@ class CsrSparseMatrix {
 
   /* matrix.h:331-397 */
   void sync2gpu(unsigned _n_gpu, enum GpuSharePolicy _policy) {
+    sblas_range range__("sblas sync2gpu (partition + upload)");
     assert(_n_gpu != 0);
     assert(_policy != none);
     release_gpu_();
@@ -467,6 +468,7 @@ class DenseMatrix {
   /* matrix.h:541-570.  replicate: every GPU gets the whole matrix; segment: GPU i gets
    * dim_gpu[i] lines of the leading dimension (columns for col_major), contiguous on the host. */
   void sync2gpu(unsigned _n_gpu, enum GpuSharePolicy _policy) {
+    sblas_range range__("sblas sync2gpu (partition + upload)");
     assert(_n_gpu != 0);
     assert(_policy != none);
     release_gpu_();
@@ -507,6 +509,24 @@ class DenseMatrix {
     if (dim > 0)
       SBLAS_SAFE_CALL(sblas_abi<DataType>::download((int)i_gpu, val_gpu[i_gpu], ld_gpu[i_gpu], (int64_t)second_order,
                                                     dim, dev_layout, val + off));
+  }
+
+  /* B200 build: sync2cpu(i) for i < n, with the downloads of all GPUs in flight together (each GPU has its own host
+   * link); what sblas_spmm_csr_v1 uses for its in-op refresh of the host copy (spmm.h:151) */
+  void sync2cpu_all(unsigned n) {
+    assert(val_gpu != NULL);
+    assert(n <= n_gpu);
+    if (policy != segment) { if (n > 0) sync2cpu(0); return; }
+    const IdxType second_order = (order == row_major) ? width : height;
+    const DataType* d[SBLAS_MAX_GPU];
+    DataType* h[SBLAS_MAX_GPU];
+    int64_t dims[SBLAS_MAX_GPU];
+    for (unsigned i = 0; i < n; i++) {
+      d[i] = val_gpu[i];
+      dims[i] = (int64_t)dim_gpu[i];
+      h[i] = val + (size_t)i * (size_t)avg_val * (size_t)second_order;
+    }
+    SBLAS_SAFE_CALL(sblas_abi<DataType>::download_multi(n, d, ld_gpu, (int64_t)second_order, dims, dev_layout, h));
   }
 
   /* matrix.h:577-593 — host transpose into a new matrix of the other major order */
@@ -625,6 +645,7 @@ class DenseVector {
 
   /* matrix.h:688-704 — vectors are always replicated */
   void sync2gpu(unsigned _n_gpu, enum GpuSharePolicy _policy) {
+    sblas_range range__("sblas sync2gpu (partition + upload)");
     assert(_n_gpu != 0);
     assert(_policy != none);
     assert(_policy != segment);

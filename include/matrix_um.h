@@ -15,8 +15,8 @@
  * B200 build specifics: dense operands stay col-major on the device (they alias the host
  * arrays), so the ops run the native col-major SpMM kernel; segment slices of col_idx / val
  * start at i*avg_nnz and are generally not 16-byte aligned, which the kernels detect (they take
- * the element-wise load path instead of the TMA bulk path).  NVTX ranges of the reference
- * (:435-445 etc.) are tracing only and are not reproduced. */
+ * the element-wise load path instead of the TMA bulk path).  NVTX ranges as in the reference
+ * (:435-445 etc.): sync2gpu, the tuning hooks and the ops push / pop named ranges (sblas_range_push). */
 #ifndef MATRIX_UM_H
 #define MATRIX_UM_H
 #ifdef MATRIX_H
@@ -99,6 +99,7 @@ class CsrSparseMatrix {
   CsrSparseMatrix& operator=(const CsrSparseMatrix&) = delete;
 
   void sync2gpu(unsigned _n_gpu, enum GpuSharePolicy _policy) { /* matrix_um.h:458-527 */
+    sblas_range range__("sblas_um sync2gpu (partition + alias)");
     assert(_n_gpu != 0);
     assert(_policy != none);
     release_gpu_();
@@ -151,14 +152,14 @@ class CsrSparseMatrix {
   }
 
   /* matrix_um.h:529-564 / :566-602 / :604-614 */
-  void applyGpuTuning(bool readOnly = true) {
+  void applyGpuTuning(bool readOnly = true) { sblas_range range__("sblas_um applyGpuTuning");
     for (unsigned i = 0; i < n_gpu; i++) {
       sblas_um_detail::tune_range(csrRowPtr_gpu[i], gpu_rp_bytes_(i), readOnly, (int)i);
       sblas_um_detail::tune_range(csrColIdx_gpu[i], gpu_nz_(i) * sizeof(IdxType), readOnly, (int)i);
       sblas_um_detail::tune_range(csrVal_gpu[i], gpu_nz_(i) * sizeof(DataType), readOnly, (int)i);
     }
   }
-  void removeGpuTuning(bool readOnly = true) {
+  void removeGpuTuning(bool readOnly = true) { sblas_range range__("sblas_um removeGpuTuning");
     for (unsigned i = 0; i < n_gpu; i++) {
       sblas_um_detail::untune_range(csrRowPtr_gpu[i], gpu_rp_bytes_(i), readOnly, (int)i, true);
       sblas_um_detail::untune_range(csrColIdx_gpu[i], gpu_nz_(i) * sizeof(IdxType), readOnly, (int)i, true);
@@ -276,6 +277,7 @@ class DenseMatrix {
   DenseMatrix& operator=(const DenseMatrix&) = delete;
 
   void sync2gpu(unsigned _n_gpu, enum GpuSharePolicy _policy) { /* matrix_um.h:760-791 */
+    sblas_range range__("sblas_um sync2gpu (partition + alias)");
     assert(_n_gpu != 0);
     assert(_policy != none);
     release_gpu_();
@@ -303,10 +305,10 @@ class DenseMatrix {
         val_gpu[i] = dim_gpu[i] > 0 ? val + (size_t)i * (size_t)avg * (size_t)second_order : NULL; /* alias, :788 */
     }
   }
-  void applyGpuTuning(bool readOnly = true) { /* matrix_um.h:793-814 */
+  void applyGpuTuning(bool readOnly = true) { sblas_range range__("sblas_um applyGpuTuning"); /* matrix_um.h:793-814 */
     for (unsigned i = 0; i < n_gpu; i++) sblas_um_detail::tune_range(val_gpu[i], gpu_bytes_(i), readOnly, (int)i);
   }
-  void removeGpuTuning(bool readOnly = true) { /* matrix_um.h:816-832 (no prefetch back) */
+  void removeGpuTuning(bool readOnly = true) { sblas_range range__("sblas_um removeGpuTuning"); /* matrix_um.h:816-832 (no prefetch back) */
     for (unsigned i = 0; i < n_gpu; i++) sblas_um_detail::untune_range(val_gpu[i], gpu_bytes_(i), readOnly, (int)i, false);
   }
   void applyCpuTuning() { sblas_um_detail::prefer_cpu(val, get_mtx_size()); }
@@ -425,6 +427,7 @@ class DenseVector {
     SAFE_FREE_MANAGED(val);
   }
   void sync2gpu(unsigned _n_gpu, enum GpuSharePolicy _policy) { /* matrix_um.h:973-999 */
+    sblas_range range__("sblas_um sync2gpu (partition + alias)");
     assert(_n_gpu != 0);
     assert(_policy != none);
     assert(_policy != segment);
@@ -440,10 +443,10 @@ class DenseVector {
       }
     }
   }
-  void applyGpuTuning(bool readOnly = true) {
+  void applyGpuTuning(bool readOnly = true) { sblas_range range__("sblas_um applyGpuTuning");
     for (unsigned i = 0; i < n_gpu; i++) sblas_um_detail::tune_range(val_gpu[i], get_vec_size(), readOnly, (int)i);
   }
-  void removeGpuTuning(bool readOnly = true) {
+  void removeGpuTuning(bool readOnly = true) { sblas_range range__("sblas_um removeGpuTuning");
     for (unsigned i = 0; i < n_gpu; i++) sblas_um_detail::untune_range(val_gpu[i], get_vec_size(), readOnly, (int)i, false);
   }
   void applyCpuTuning() { sblas_um_detail::prefer_cpu(val, get_vec_size()); }

@@ -44,6 +44,13 @@ SBLAS_API int sblas_device_count(void);
 /* number of CUDA kernels this library has launched so far in this process */
 SBLAS_API unsigned long long sblas_launch_count(void);
 
+/* NVTX ranges around the phases of the path (the reference marks its load / distribute / tuning phases with
+ * nvtxRangePush / Pop in matrix_um.h:435-445, :485-519, :738-741 and its UM drivers): partition + upload in
+ * sync2gpu, the tuning hooks, each op, and inside the multi-GPU ops the compute and the finish / stitch-wait phases.
+ * No-ops unless a profiler is attached.  Return the nesting level like nvtxRangePushA / nvtxRangePop. */
+SBLAS_API int sblas_range_push(const char* name);
+SBLAS_API int sblas_range_pop(void);
+
 /* ---- launch options ------------------------------------------------------------ */
 enum {
   SBLAS_VARIANT_AUTO = 0,
@@ -351,6 +358,14 @@ SBLAS_API int sblas_dense_download_f64(int gpu, const double* d, int64_t ld, int
                                        int64_t dim, int32_t dev_layout, double* h);
 SBLAS_API int sblas_dense_download_f32(int gpu, const float* d, int64_t ld, int64_t second,
                                        int64_t dim, int32_t dev_layout, float* h);
+/* DenseMatrix::sync2cpu of every GPU's slice in one call (sblas_spmm_csr_v1 downloads all the C slices inside the
+ * op, spmm.h:151 -> matrix.h:599-606): slice i (dim[i] lines of `second` elements, device pointer d[i] on logical
+ * GPU i, pitch ld[i]) -> host pointer h[i].  All downloads are enqueued before any is waited for, so the GPUs' host
+ * links work in parallel; returns when every slice is on the host.  h should be pinned (sblas_host_alloc). */
+SBLAS_API int sblas_dense_download_multi_f64(unsigned n_gpu, const double* const* d, const int64_t* ld, int64_t second,
+                                             const int64_t* dim, int32_t dev_layout, double* const* h);
+SBLAS_API int sblas_dense_download_multi_f32(unsigned n_gpu, const float* const* d, const int64_t* ld, int64_t second,
+                                             const int64_t* dim, int32_t dev_layout, float* const* h);
 /* The same two moves for a caller that re-sends a dense operand on every step (what a solver loop around
  * sblas_spmm_csr_v2 does with B.sync2gpu / C.sync2cpu, spmm_test.cu:68-84), streamed and allocation-free:
  * rows [r0, r0 + nr) of the col-major HOST matrix h (element (r, n) at h[n*h_ld + r], k columns; pinned memory

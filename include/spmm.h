@@ -73,6 +73,7 @@ inline void sblas_require_col_major_(const DenseMatrix<IdxType, DataType>* pB, c
 template <typename IdxType, typename DataType>
 void sblas_spmm_csr_v1(CsrSparseMatrix<IdxType, DataType>* pA, DenseMatrix<IdxType, DataType>* pB,
                        DenseMatrix<IdxType, DataType>* pC, DataType alpha, DataType beta, unsigned n_gpu SBLAS_TUNING_PARAM) {
+  sblas_range range__("sblas_spmm_csr_v1");
   SBLAS_TUNING_USE; /* the reference only uses it to advise its C_copy temporary (spmv_um.h:51-53), which no longer exists */
   assert(pA->width == pB->height);
   assert(pA->height == pC->height);
@@ -88,13 +89,18 @@ void sblas_spmm_csr_v1(CsrSparseMatrix<IdxType, DataType>* pA, DenseMatrix<IdxTy
       n_gpu, (int32_t)pA->height, (int32_t)pA->width, (int32_t)pA->nnz, (const int32_t* const*)pA->csrRowPtr_gpu,
       (const int32_t* const*)pA->csrColIdx_gpu, pA->csrVal_gpu, (const int32_t*)pB->dim_gpu, pB->dev_layout,
       pB->val_gpu, pB->ld_gpu, pC->val_gpu, pC->ld_gpu, alpha, beta, pA->plan_gpu));
-  for (unsigned i = 0; i < n_gpu; i++) pC->sync2cpu(i); /* spmm.h:151 */
+#ifdef SBLAS_UM
+  for (unsigned i = 0; i < n_gpu; i++) pC->sync2cpu(i); /* spmm.h:151; managed memory: nothing is copied */
+#else
+  pC->sync2cpu_all(n_gpu); /* spmm.h:151 for every GPU, the slices' downloads in flight together */
+#endif
 }
 
 /* method 2 */
 template <typename IdxType, typename DataType>
 void sblas_spmm_csr_v2(CsrSparseMatrix<IdxType, DataType>* pA, DenseMatrix<IdxType, DataType>* pB,
                        DenseMatrix<IdxType, DataType>* pC, DataType alpha, DataType beta, unsigned n_gpu SBLAS_TUNING_PARAM) {
+  sblas_range range__("sblas_spmm_csr_v2");
   SBLAS_TUNING_USE; /* the reference only uses it to advise its C_copy temporary (spmv_um.h:51-53), which no longer exists */
   assert(pA->width == pB->height);
   assert(pA->height == pC->height);

@@ -42,6 +42,7 @@ void sblas_spmv_csr_cpu(CsrSparseMatrix<IdxType, DataType>* pA, DenseVector<IdxT
 template <typename IdxType, typename DataType>
 void sblas_spmv_csr_v1(CsrSparseMatrix<IdxType, DataType>* pA, DenseVector<IdxType, DataType>* pB,
                        DenseVector<IdxType, DataType>* pC, DataType alpha, DataType beta, unsigned n_gpu SBLAS_TUNING_PARAM) {
+  sblas_range range__("sblas_spmv_csr_v1");
   SBLAS_TUNING_USE; /* the reference only uses it to advise its C_copy temporary (spmv_um.h:51-53), which no longer exists */
   assert(pA->width == pB->length);  /* spmv.h:40 */
   assert(pA->height == pC->length); /* spmv.h:41 */

@@ -206,10 +206,19 @@ IdxType csr_findRowIdxUsingNnzIdx(const IdxType* rowPtr, IdxType height, IdxType
 }
 
 /* ---- f32 / f64 dispatch onto the C ABI ------------------------------------------------------ */
+/* scoped NVTX range (sblas_range_push / _pop) */
+struct sblas_range {
+  explicit sblas_range(const char* name) { sblas_range_push(name); }
+  ~sblas_range() { sblas_range_pop(); }
+  sblas_range(const sblas_range&) = delete;
+  sblas_range& operator=(const sblas_range&) = delete;
+};
+
 template <typename DataType> struct sblas_abi; /* only float and double (utility.h:304-306) */
 template <> struct sblas_abi<double> {
   static int upload(int g, const double* h, int64_t second, int64_t dim, int32_t lay, double** d, int64_t* ld) { return sblas_dense_upload_f64(g, h, second, dim, lay, d, ld); }
   static int download(int g, const double* d, int64_t ld, int64_t second, int64_t dim, int32_t lay, double* h) { return sblas_dense_download_f64(g, d, ld, second, dim, lay, h); }
+  static int download_multi(unsigned n, const double* const* d, const int64_t* ld, int64_t second, const int64_t* dim, int32_t lay, double* const* h) { return sblas_dense_download_multi_f64(n, d, ld, second, dim, lay, h); }
   static int axpby(double* v0, const double* v1, double a, double b, int64_t n) { return sblas_axpby_f64(NULL, v0, v1, a, b, n); }
   static int spmv_v1(unsigned n, int32_t h, int32_t w, const int32_t* const* rp, const int32_t* const* ci, const double* const* v, const int32_t* ng, const int32_t* s, const int32_t* e, const double* const* x, double* const* y, double a, double b, const sblasPlan_t* p) { return sblas_mgpu_spmv_csr_v1_f64(n, h, w, rp, ci, v, ng, s, e, x, y, a, b, p); }
   static int spmm_v1(unsigned n, int32_t h, int32_t w, int32_t nnz, const int32_t* const* rp, const int32_t* const* ci, const double* const* v, const int32_t* dim, int32_t lay, const double* const* B, const int64_t* ldb, double* const* C, const int64_t* ldc, double a, double b, const sblasPlan_t* p) { return sblas_mgpu_spmm_csr_v1_f64(n, h, w, nnz, rp, ci, v, dim, lay, B, ldb, C, ldc, a, b, p); }
@@ -218,6 +227,7 @@ template <> struct sblas_abi<double> {
 template <> struct sblas_abi<float> {
   static int upload(int g, const float* h, int64_t second, int64_t dim, int32_t lay, float** d, int64_t* ld) { return sblas_dense_upload_f32(g, h, second, dim, lay, d, ld); }
   static int download(int g, const float* d, int64_t ld, int64_t second, int64_t dim, int32_t lay, float* h) { return sblas_dense_download_f32(g, d, ld, second, dim, lay, h); }
+  static int download_multi(unsigned n, const float* const* d, const int64_t* ld, int64_t second, const int64_t* dim, int32_t lay, float* const* h) { return sblas_dense_download_multi_f32(n, d, ld, second, dim, lay, h); }
   static int axpby(float* v0, const float* v1, float a, float b, int64_t n) { return sblas_axpby_f32(NULL, v0, v1, a, b, n); }
   static int spmv_v1(unsigned n, int32_t h, int32_t w, const int32_t* const* rp, const int32_t* const* ci, const float* const* v, const int32_t* ng, const int32_t* s, const int32_t* e, const float* const* x, float* const* y, float a, float b, const sblasPlan_t* p) { return sblas_mgpu_spmv_csr_v1_f32(n, h, w, rp, ci, v, ng, s, e, x, y, a, b, p); }
   static int spmm_v1(unsigned n, int32_t h, int32_t w, int32_t nnz, const int32_t* const* rp, const int32_t* const* ci, const float* const* v, const int32_t* dim, int32_t lay, const float* const* B, const int64_t* ldb, float* const* C, const int64_t* ldc, float a, float b, const sblasPlan_t* p) { return sblas_mgpu_spmm_csr_v1_f32(n, h, w, nnz, rp, ci, v, dim, lay, B, ldb, C, ldc, a, b, p); }

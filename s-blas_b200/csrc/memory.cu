@@ -7,6 +7,7 @@
 // through these entry points, so they compile with a plain C++ compiler (no CUDA toolkit on
 // the include path) and every CUDA call of the product lives inside libsblas_b200.so.
 // `gpu` is always a LOGICAL GPU ordinal (sblas_device_of).
+#include <nvtx3/nvToolsExt.h>
 #include <stdlib.h>
 
 #include <algorithm>
@@ -189,10 +190,48 @@ static int download_rows(cudaStream_t st, const T* d_src, int64_t ld, int64_t nr
   return 0;
 }
 
+// DenseMatrix::sync2cpu of EVERY GPU's slice at once (what sblas_spmm_csr_v1 does after its kernels, spmm.h:151):
+// the downloads of all GPUs are enqueued first (each on its own device: layout conversion chunks + D2H copies over
+// that GPU's own host link), then all devices are synchronised — n host links in parallel instead of n serial
+// cudaMemcpy calls with a staging cudaMalloc / cudaFree each.
+template <typename T>
+static int dense_download_multi(unsigned n_gpu, const T* const* d, const int64_t* ld, int64_t second, const int64_t* dim,
+                                int32_t layout, T* const* h) {
+  SBLAS_CHECK(n_gpu >= 1 && n_gpu <= SBLAS_MAX_GPU && d && ld && dim && h, "dense_download_multi: bad arguments");
+  int rc = 0;
+  for (unsigned i = 0; i < n_gpu && rc == 0; ++i) {
+    if (dim[i] <= 0 || second <= 0) continue;
+    SBLAS_CHECK(d[i] && h[i], "dense_download_multi: null pointer for GPU %u", i);
+    SBLAS_ON_GPU((int)i);
+    if (layout == SBLAS_COL_MAJOR) {
+      SBLAS_CHECK(ld[i] == second, "dense_download_multi: col-major slices are contiguous (ld == rows)");
+      SBLAS_CUDA(cudaMemcpyAsync(h[i], d[i], sizeof(T) * (size_t)second * (size_t)dim[i], cudaMemcpyDeviceToHost, nullptr));
+    } else {
+      rc = download_rows<T>(nullptr, d[i], ld[i], second, (int32_t)dim[i], h[i], second, 0);
+    }
+  }
+  for (unsigned i = 0; i < n_gpu; ++i) {
+    if (dim[i] <= 0 || second <= 0) continue;
+    SBLAS_ON_GPU((int)i);
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e != cudaSuccess && rc == 0) { set_error("dense_download_multi: GPU %u: %s", i, cudaGetErrorString(e)); rc = 1; }
+  }
+  return rc;
+}
+
 }  // namespace sblas
 
 using namespace sblas;
 extern "C" {
+
+int sblas_dense_download_multi_f64(unsigned n_gpu, const double* const* d, const int64_t* ld, int64_t second,
+                                   const int64_t* dim, int32_t dev_layout, double* const* h) {
+  return dense_download_multi<double>(n_gpu, d, ld, second, dim, dev_layout, h);
+}
+int sblas_dense_download_multi_f32(unsigned n_gpu, const float* const* d, const int64_t* ld, int64_t second,
+                                   const int64_t* dim, int32_t dev_layout, float* const* h) {
+  return dense_download_multi<float>(n_gpu, d, ld, second, dim, dev_layout, h);
+}
 
 int sblas_dense_upload_rows_f64(void* stream, const double* h, int64_t h_ld, int64_t r0, int64_t nr, int32_t k,
                                 double* d_dst, int64_t ld) {
@@ -210,6 +249,11 @@ int sblas_dense_download_rows_f32(void* stream, const float* d_src, int64_t ld, 
                                   int64_t h_ld, int64_t r0) {
   return download_rows<float>((cudaStream_t)stream, d_src, ld, nr, k, h, h_ld, r0);
 }
+
+// NVTX ranges (matrix_um.h:30, :435-445, :485-519 of the reference mark its load / distribute / tuning phases):
+// nvtx3 is header-only and costs a null-pointer test per call unless a tool (nsys, ncu --nvtx) is attached
+int sblas_range_push(const char* name) { return nvtxRangePushA(name ? name : "sblas"); }
+int sblas_range_pop(void) { return nvtxRangePop(); }
 
 int sblas_host_alloc(size_t bytes, void** p) {
   SBLAS_CHECK(p, "host_alloc: null out pointer");

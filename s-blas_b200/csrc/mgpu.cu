@@ -20,6 +20,13 @@
 
 namespace sblas {
 
+// NVTX range of the current phase of an op; closed on every exit path
+struct PhaseRange {
+  explicit PhaseRange(const char* name) { sblas_range_push(name); }
+  void next(const char* name) { sblas_range_pop(); sblas_range_push(name); }
+  ~PhaseRange() { sblas_range_pop(); }
+};
+
 struct FinishList {
   int n_shared;
   int32_t row[SBLAS_MAX_GPU], first[SBLAS_MAX_GPU], last[SBLAS_MAX_GPU];
@@ -230,6 +237,7 @@ static int mgpu_rowsplit(unsigned n_gpu, int32_t height, int32_t width,
   int rc = 0;
 
   // 1. every GPU: its segment, fused epilogue, stores into all replicas
+  PhaseRange phase("sblas mgpu: segment kernels + fused peer stitch");
   for (unsigned i = 0; i < n_gpu && rc == 0; ++i) {
     if (!active[i]) continue;
     SBLAS_CUDA(cudaSetDevice(device_of(i)));
@@ -275,6 +283,7 @@ static int mgpu_rowsplit(unsigned n_gpu, int32_t height, int32_t width,
     }
     SBLAS_CUDA(cudaEventRecord(ctx->ev[i], nullptr));
   }
+  phase.next("sblas mgpu: carries + finish rows + device sync");
   // 2. every GPU: wait for all segments (and carries / panel copies), then finish the shared
   //    and the uncovered rows of its own replica.  Step 1 never writes those rows with new
   //    values (a panel copy can only carry their old value), so running this last is enough.

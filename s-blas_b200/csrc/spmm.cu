@@ -415,6 +415,17 @@ __device__ __forceinline__ float4 lds_v(uint32_t a, float4) {
   return r;
 }
 
+__device__ __forceinline__ void sts_v(uint32_t a, const double2& v) {
+  asm volatile("st.shared.v2.f64 [%0], {%1,%2};" ::"r"(a), "d"(v.x), "d"(v.y) : "memory");
+}
+__device__ __forceinline__ void sts_v(uint32_t a, const float4& v) {
+  asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(a), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+// shared (32-bit address) -> global bulk copy, see bulk_s2g
+__device__ __forceinline__ void bulk_s2g_a(void* gdst, uint32_t ssrc, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(ssrc), "r"(bytes) : "memory");
+}
+
 // U blocks whose {col,mask} entries start at shared address a_cm and values at a_val (TAIL: only
 // the first n < U exist): gathers first, then the multiply-adds; a branch takes an unpredicated
 // body when all U masks are full.  bb[nb] = this lane's (clamped, always valid) column of slice nb
@@ -472,7 +483,11 @@ template <typename T, int VEC, int NB, int R, bool EXACT, int NSTAGE>
 __global__ void __launch_bounds__(kRbpBlock, (R == 4 ? 4 : 3) - NB)
 spmm_rbp_kernel(int64_t n_blockrows, const int32_t* __restrict__ blk_ptr, const int2* __restrict__ colmask,
                 const T* __restrict__ bval, const T* __restrict__ B, uint32_t ldb_bytes, MatSink<T> sink,
-                int32_t cap_blocks, int32_t kp, int32_t logP, int32_t prefetch) {
+                int32_t cap_blocks, int32_t kp, int32_t logP, int32_t prefetch, int32_t bulk) {
+  // bulk: 0 = every lane stores its result slices itself (st.global to C and to every replica);
+  //       1 = the results are parked in the warp's C buffer (the old C values they replace) and lane 0 pushes each
+  //           512-byte row slice to every REPLICA with one TMA bulk store (the stitch of method 2 leaves the LSU);
+  //       2 = ... and to the local C as well (no st.global left in the epilogue)
   using V = typename VecT<T, VEC>::type;
   constexpr int U = NB == 1 ? 4 : 2;
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -587,6 +602,10 @@ spmm_rbp_kernel(int64_t n_blockrows, const int32_t* __restrict__ blk_ptr, const 
     if (br < n_blockrows) {
       const int32_t p0a = lds_i1(st_a + off_ptr) & ~1;
       const int2 bp = make_int2(lds_i1(st_a + off_ptr + w * 4), lds_i1(st_a + off_ptr + w * 4 + 4));
+      if (bulk) {   // the bulk stores of the previous tile have read the C buffer before it is refilled
+        if (lane == 0) bulk_wait_read_all();
+        __syncwarp();
+      }
       // old C values of my R rows: LDGSTS past L1 now, read back in the epilogue
 #pragma unroll
       for (int r = 0; r < R; ++r) {
@@ -627,10 +646,40 @@ spmm_rbp_kernel(int64_t n_blockrows, const int32_t* __restrict__ blk_ptr, const 
               const int64_t off = row * sink.ldc + c0;
               const V cv = lds_v(a_C + (uint32_t)((r * NB + nb) * 512), V());
               const V res = vaxpby(sink.alpha, acc[r][nb], sink.beta, cv);
-              *reinterpret_cast<V*>(sink.C + off) = res;
-              for (int d = 0; d < sink.out.n; ++d) *reinterpret_cast<V*>(sink.out.ptr[d] + off) = res;
+              if (bulk) {
+                sts_v(a_C + (uint32_t)((r * NB + nb) * 512), res);
+                if (bulk == 1) *reinterpret_cast<V*>(sink.C + off) = res;
+              } else {
+                *reinterpret_cast<V*>(sink.C + off) = res;
+                for (int d = 0; d < sink.out.n; ++d) *reinterpret_cast<V*>(sink.out.ptr[d] + off) = res;
+              }
             }
           }
+        }
+      }
+      if (bulk) {
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+          const int wc0 = p * NB * 32 * VEC;                 // first column of the warp's slices
+          const uint32_t a_W = a_C - (uint32_t)(lane * 16);
+#pragma unroll
+          for (int r = 0; r < R; ++r) {
+            const int64_t row = br * R + r;
+            if (row >= sink.rows) break;
+            if (sink.partial_slot((int32_t)row) >= 0) continue;
+#pragma unroll
+            for (int nb = 0; nb < NB; ++nb) {
+              const int c0 = wc0 + nb * 32 * VEC;
+              if (c0 >= kp) break;
+              const uint32_t bytes = (uint32_t)min(32 * VEC, kp - c0) * (uint32_t)sizeof(T);
+              const int64_t off = row * sink.ldc + c0;
+              const uint32_t src = a_W + (uint32_t)((r * NB + nb) * 512);
+              if (bulk == 2) bulk_s2g_a(sink.C + off, src, bytes);
+              for (int d = 0; d < sink.out.n; ++d) bulk_s2g_a(sink.out.ptr[d] + off, src, bytes);
+            }
+          }
+          bulk_commit();
         }
       }
     }
@@ -638,6 +687,7 @@ spmm_rbp_kernel(int64_t n_blockrows, const int32_t* __restrict__ blk_ptr, const 
     __syncwarp();
     if (lane == 0) mbar_arrive(&empty[s]);
   }
+  if (bulk && lane == 0) bulk_wait_all();   // every row slice has landed (locally and on the peers) before the warp retires
 }
 
 // P = column slices per CTA (1, 2, 4); panel = P*NB*32*VEC columns per pass over A
@@ -679,8 +729,15 @@ static int launch_rbp_r(cudaStream_t st, const sblasPlan_st* plan, int NB, int l
   const int32_t prefetch = ((sink.flags & SBLAS_FLAG_NO_PREFETCH_B) ? 0
                             : ((sink.flags & SBLAS_FLAG_PREFETCH_B) || (NB <= 1 && logP == 0)) ? 1 : 0) |
                            ((sink.flags & SBLAS_FLAG_PREFETCH_C) ? 2 : 0);
+  // epilogue stores: TMA bulk stores of the 512-byte row slices when the rows go to replicas too (needs a 16-byte
+  // row pitch); SBLAS_RBP_BULK=0/1/2 overrides (2: the local C as well), SBLAS_FLAG_STITCH_DIRECT keeps per-lane stores
+  static const int env_bulk = [] { const char* e = getenv("SBLAS_RBP_BULK"); return e ? atoi(e) : -1; }();
+  int32_t bulk = env_bulk >= 0 ? env_bulk : (sink.out.n > 0 ? 1 : 0);
+  if ((sink.flags & SBLAS_FLAG_STITCH_DIRECT) || (sink.ldc * (int64_t)sizeof(T)) % 16 != 0) bulk = 0;
+  for (int d = 0; d < sink.out.n; ++d)
+    if (!aligned16(sink.out.ptr[d])) bulk = 0;
   void* args[] = {(void*)&rb.n_blockrows, (void*)&rb.d_ptr, (void*)&cm, (void*)&bv, (void*)&B, (void*)&ldb_bytes,
-                  (void*)&sink, (void*)&cap_blocks, (void*)&kp, (void*)&logP, (void*)&prefetch};
+                  (void*)&sink, (void*)&cap_blocks, (void*)&kp, (void*)&logP, (void*)&prefetch, (void*)&bulk};
   SBLAS_CUDA(cudaLaunchKernel(kern, dim3(grid), dim3(kRbpBlock), args, smem, st));
   ++g_launches;
   return 0;

@@ -1202,10 +1202,17 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
         // sliced-ELL panels: one CTA per window of 256 rows, persistent over the windows
         const ColPanels::Sell& sl = cp.sell[(size_t)p];
         const int n_win = sl.n_slices / (kSellSigma / kSellC);
-        const void* kern = (const void*)spmv_sell_kernel<T, 4>;
+        // entries in flight per lane: SBLAS_SELL_U = 2 / 4 / 8 (default 8: c3v 2.95 / 2.83 / 2.77 ms, profiles/r02_exp_c3v_sell_u_grid.log)
+        static const int env_u = [] { const char* e = getenv("SBLAS_SELL_U"); return e ? atoi(e) : 8; }();
+        const void* kern = env_u == 8 ? (const void*)spmv_sell_kernel<T, 8> : env_u == 2 ? (const void*)spmv_sell_kernel<T, 2>
+                                                                                          : (const void*)spmv_sell_kernel<T, 4>;
         int per_sm = 0, n_sm = kNumSM;
         if ((rc = kernel_residency(kern, kSellSigma, 0, &per_sm, &n_sm)) != 0) break;
-        const int grid = std::max(1, std::min(n_win, n_sm * per_sm));
+        static const int env_g = [] { const char* e = getenv("SBLAS_SELL_GRID"); return e ? atoi(e) : 0; }();   // CTAs per SM (experiments)
+        const int grid = std::max(1, std::min(n_win, n_sm * (env_g > 0 ? std::min(env_g, per_sm) : per_sm)));
+        if (env_u == 8) spmv_sell_kernel<T, 8><<<grid, kSellSigma, 0, st>>>(sl.n_slices, sl.d_sptr, sl.d_perm, sl.d_col, (const T*)sl.d_val, x, ps);
+        else if (env_u == 2) spmv_sell_kernel<T, 2><<<grid, kSellSigma, 0, st>>>(sl.n_slices, sl.d_sptr, sl.d_perm, sl.d_col, (const T*)sl.d_val, x, ps);
+        else
         spmv_sell_kernel<T, 4><<<grid, kSellSigma, 0, st>>>(sl.n_slices, sl.d_sptr, sl.d_perm, sl.d_col, (const T*)sl.d_val, x, ps);
         ++g_launches;
         cudaError_t e = cudaGetLastError();

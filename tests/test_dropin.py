@@ -51,7 +51,7 @@ def test_headers_only_use_exported_symbols(built):
         used |= set(re.findall(r"\b(sblas_[a-z0-9_]+)\s*\(", src))
     local = {"sblas_safe_call_", "sblas_cuda_safe_call_", "sblas_cuda_check_error_", "sblas_sync_gpus",
              "sblas_default_dense_device_layout", "sblas_require_col_major_", "sblas_spmv_csr_cpu",
-             "sblas_spmv_csr_v1", "sblas_spmm_csr_cpu", "sblas_spmm_csr_v1", "sblas_spmm_csr_v2"}
+             "sblas_spmv_csr_v1", "sblas_spmm_csr_cpu", "sblas_spmm_csr_v1", "sblas_spmm_csr_v2", "sblas_range"}
     missing = sorted(u for u in used - local if u not in exported)
     assert not missing, missing
 
