@@ -86,6 +86,8 @@ enum {
   SBLAS_FLAG_STITCH_DIRECT = 2048, /* replicas (sblasOpts.replica) are written by the computing lanes' own st.global
                                   instead of TMA bulk stores of staged row chunks (the default for wide SpMM rows):
                                   needed for NVSwitch multicast addresses, kept as the comparison point */
+  SBLAS_FLAG_STITCH_BULK = 4096, /* SBLAS_SPMM_ROWBLOCK_PIPE: replicas written by TMA bulk stores of the 512-byte row
+                                  slices parked in the warp's C buffer (measured level with the per-lane stores: opt-in) */
   SBLAS_FLAG_HEAD_PARTIAL = 2, /* local row 0 continues a row begun on the previous GPU
                                   (matrix.h:443-445): its sum goes to carry[0..k), not to y/C */
   SBLAS_FLAG_TAIL_PARTIAL = 4, /* local last row continues on the next GPU: sum -> carry[k..2k) */

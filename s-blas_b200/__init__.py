@@ -13,7 +13,7 @@ Layout:
   synth.py     device-side synthetic inputs of BASELINE.json's configs
 """
 from . import _lib, dist, kernels, matrix, ops, synth, synth_np  # noqa: F401
-from ._lib import (COL_MAJOR, FLAG_EXACT, FLAG_FMA, FLAG_HEAD_PARTIAL, FLAG_NO_L1, FLAG_NO_PREFETCH_B, FLAG_PREFETCH_B, FLAG_PREFETCH_C, FLAG_SPLIT_MERGE, FLAG_SPLIT_SEG, FLAG_SPLIT_SERIAL, FLAG_STITCH_DIRECT, FLAG_TAIL_PARTIAL,  # noqa: F401
+from ._lib import (COL_MAJOR, FLAG_EXACT, FLAG_FMA, FLAG_HEAD_PARTIAL, FLAG_NO_L1, FLAG_NO_PREFETCH_B, FLAG_PREFETCH_B, FLAG_PREFETCH_C, FLAG_SPLIT_MERGE, FLAG_SPLIT_SEG, FLAG_SPLIT_SERIAL, FLAG_STITCH_BULK, FLAG_STITCH_DIRECT, FLAG_TAIL_PARTIAL,  # noqa: F401
                    ROW_MAJOR, SPMM_COLMAJOR, SPMM_ROWBLOCK, SPMM_ROWBLOCK_PIPE, SPMM_ROWBLOCK_TILEB, SPMM_ROWMAJOR, SPMV_COLPANEL, SPMV_PIPE, SPMV_SPLIT, SPMV_TILE, SPMV_VECTOR,
                    SblasError, make_opts)
 from .matrix import (CooSparseMatrix, CscSparseMatrix, CscToCsr, CsrSparseMatrix, CsrToCsc, DenseMatrix,  # noqa: F401

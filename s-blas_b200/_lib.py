@@ -20,6 +20,7 @@ FLAG_SPLIT_SEG = 256
 FLAG_PREFETCH_C = 512
 FLAG_EXACT = 1024
 FLAG_STITCH_DIRECT = 2048
+FLAG_STITCH_BULK = 4096
 ROW_MAJOR, COL_MAJOR = 0, 1
 
 

@@ -36,16 +36,22 @@ struct FinishList {
 
 // out[row, n] = beta*out[row, n] + alpha * (carry[first][tail][n] + sum_{g>first} carry[g][head][n])
 // and out[r, n] = beta*out[r, n] + alpha*0 for rows no segment covers.
+// tab[g] = the carry table ([gpu][head|tail][kpad]) in which GPU g's carries are found: with peer access GPU g's OWN
+// table, read over NVLink by the finish kernel of every other GPU (a few hundred bytes; this removes the n*(n-1)
+// cudaMemcpyPeerAsync calls per op that cost 0.5 ms of host time at 8 GPUs); else the local copy of it
+template <typename T>
+struct CarryTabs { const T* tab[SBLAS_MAX_GPU]; };
+
 template <typename T>
 __global__ void __launch_bounds__(256)
-finish_rows_kernel(FinishList fl, const T* __restrict__ carry, int32_t kpad, int32_t k,
+finish_rows_kernel(FinishList fl, CarryTabs<T> ct, int32_t kpad, int32_t k,
                    int32_t layout, T* out, int64_t ld, T alpha, T beta) {
   const int64_t tid = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   const int64_t nth = (int64_t)gridDim.x * blockDim.x;
   for (int64_t e = tid; e < (int64_t)fl.n_shared * k; e += nth) {
     const int s = (int)(e / k), n = (int)(e % k);
-    T sum = carry[((int64_t)fl.first[s] * 2 + 1) * kpad + n];
-    for (int g = fl.first[s] + 1; g <= fl.last[s]; ++g) sum += carry[((int64_t)g * 2) * kpad + n];
+    T sum = ct.tab[fl.first[s]][((int64_t)fl.first[s] * 2 + 1) * kpad + n];
+    for (int g = fl.first[s] + 1; g <= fl.last[s]; ++g) sum += ct.tab[g][((int64_t)g * 2) * kpad + n];
     const int64_t off = layout == SBLAS_ROW_MAJOR ? (int64_t)fl.row[s] * ld + n : (int64_t)n * ld + fl.row[s];
     out[off] = axpby_rn(alpha, sum, beta, out[off]);
   }
@@ -61,13 +67,13 @@ finish_rows_kernel(FinishList fl, const T* __restrict__ carry, int32_t kpad, int
 }
 
 template <typename T>
-static int launch_finish(cudaStream_t st, const FinishList& fl, const T* carry, int32_t kpad,
+static int launch_finish(cudaStream_t st, const FinishList& fl, const CarryTabs<T>& ct, int32_t kpad,
                          int32_t k, int32_t layout, T* out, int64_t ld, T alpha, T beta) {
   int64_t work = (int64_t)fl.n_shared * k;
   for (int g = 0; g < fl.n_gap; ++g) work = std::max<int64_t>(work, ((int64_t)fl.gap_hi[g] - fl.gap_lo[g]) * k);
   if (work <= 0) return 0;
   const int blocks = (int)std::min<int64_t>(ceil_div(work, 256), kNumSM * 8);
-  finish_rows_kernel<T><<<blocks, 256, 0, st>>>(fl, carry, kpad, k, layout, out, ld, alpha, beta);
+  finish_rows_kernel<T><<<blocks, 256, 0, st>>>(fl, ct, kpad, k, layout, out, ld, alpha, beta);
   SBLAS_LAUNCH_CHECK();
   return 0;
 }
@@ -262,8 +268,9 @@ static int mgpu_rowsplit(unsigned n_gpu, int32_t height, int32_t width,
                ? sblas_spmv_csr_f64(nullptr, rows, width, nnz_gpu[i], rp[i], ci[i], (const double*)val[i], (const double*)B[i], (double*)(C[i] + row_off), alpha, beta, plan, &o)
                : sblas_spmv_csr_f32(nullptr, rows, width, nnz_gpu[i], rp[i], ci[i], (const float*)val[i], (const float*)B[i], (float*)(C[i] + row_off), alpha, beta, plan, &o);
     if (rc) break;
-    // carries of GPU i to every other GPU's carry table (tiny)
-    if (head[i] || tail[i])
+    // carries of GPU i to every other GPU's carry table (tiny) — only without peer access: with it the finish
+    // kernels read them in place
+    if (!peer && (head[i] || tail[i]))
       for (unsigned d = 0; d < n_gpu; ++d)
         if (d != i)
           SBLAS_CUDA(cudaMemcpyPeerAsync((T*)ctx->carry[d] + (size_t)i * 2 * kpad, device_of(d), carry_i, device_of(i),
@@ -291,7 +298,9 @@ static int mgpu_rowsplit(unsigned n_gpu, int32_t height, int32_t width,
     SBLAS_CUDA(cudaSetDevice(device_of(d)));
     for (unsigned i = 0; i < n_gpu; ++i)
       if (i != d && active[i]) SBLAS_CUDA(cudaStreamWaitEvent(nullptr, ctx->ev[i], 0));
-    rc = launch_finish<T>(nullptr, fl, (const T*)ctx->carry[d], kpad, k, layout, C[d], ldc, alpha, beta);
+    CarryTabs<T> ct;
+    for (unsigned g = 0; g < SBLAS_MAX_GPU; ++g) ct.tab[g] = (const T*)ctx->carry[(peer && g < n_gpu) ? g : d];
+    rc = launch_finish<T>(nullptr, fl, ct, kpad, k, layout, C[d], ldc, alpha, beta);
   }
   for (unsigned d = 0; d < n_gpu; ++d) {
     cudaSetDevice(device_of(d));
@@ -424,7 +433,9 @@ SBLAS_MGPU_SPMM(f32, float)
     fl.n_gap = 0;                                                                                  \
     fl.n_shared = n_shared;                                                                        \
     for (int i = 0; i < n_shared; ++i) { fl.row[i] = rows[i]; fl.first[i] = first[i]; fl.last[i] = last[i]; } \
-    return launch_finish<T>((cudaStream_t)stream, fl, d_carry, (k + 3) & ~3, k, layout, d_out, ld, \
+    CarryTabs<T> ct;                                                                               \
+    for (int g = 0; g < SBLAS_MAX_GPU; ++g) ct.tab[g] = d_carry;                                   \
+    return launch_finish<T>((cudaStream_t)stream, fl, ct, (k + 3) & ~3, k, layout, d_out, ld,      \
                             alpha, beta);                                                          \
   }
 SBLAS_FIXUP(f64, double)

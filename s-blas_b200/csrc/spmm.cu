@@ -729,10 +729,13 @@ static int launch_rbp_r(cudaStream_t st, const sblasPlan_st* plan, int NB, int l
   const int32_t prefetch = ((sink.flags & SBLAS_FLAG_NO_PREFETCH_B) ? 0
                             : ((sink.flags & SBLAS_FLAG_PREFETCH_B) || (NB <= 1 && logP == 0)) ? 1 : 0) |
                            ((sink.flags & SBLAS_FLAG_PREFETCH_C) ? 2 : 0);
-  // epilogue stores: TMA bulk stores of the 512-byte row slices when the rows go to replicas too (needs a 16-byte
-  // row pitch); SBLAS_RBP_BULK=0/1/2 overrides (2: the local C as well), SBLAS_FLAG_STITCH_DIRECT keeps per-lane stores
-  static const int env_bulk = [] { const char* e = getenv("SBLAS_RBP_BULK"); return e ? atoi(e) : -1; }();
-  int32_t bulk = env_bulk >= 0 ? env_bulk : (sink.out.n > 0 ? 1 : 0);
+  // epilogue stores: per-lane st.global by default.  TMA bulk stores of the 512-byte row slices (SBLAS_RBP_BULK=1:
+  // to the replicas, =2: to the local C as well; needs a 16-byte row pitch) are parity-tested but measured level or
+  // slower: b32m 1 GPU 8.44 -> 8.72 ms (=2), 2 GPUs 7.05 -> 7.16 ms, 4 GPUs 9.70 -> 9.77 ms (=1)
+  // (profiles/r02_exp_b32m_rbp_bulk_n1.log, r02_bench_b32m_n{2,4}*.json): a 512-byte slice is too small a TMA
+  // transaction to beat 32 coalesced 16-byte stores, unlike the 16-32 KB chunks of the CSR kernel's stitch.
+  static const int env_bulk = [] { const char* e = getenv("SBLAS_RBP_BULK"); return e ? atoi(e) : 0; }();
+  int32_t bulk = env_bulk > 0 ? env_bulk : ((sink.flags & SBLAS_FLAG_STITCH_BULK) && sink.out.n > 0 ? 1 : 0);
   if ((sink.flags & SBLAS_FLAG_STITCH_DIRECT) || (sink.ldc * (int64_t)sizeof(T)) % 16 != 0) bulk = 0;
   for (int d = 0; d < sink.out.n; ++d)
     if (!aligned16(sink.out.ptr[d])) bulk = 0;

@@ -334,9 +334,10 @@ def test_rowblock_height_selection(sblas, dev):
         assert (R if nb else 0) == want, (kind, R, nb, fill)
 
 
-@pytest.mark.parametrize("piped", [False, True])
+@pytest.mark.parametrize("piped", [False, True, "bulk"])
 def test_spmm_rowblock_partials_and_replicas(sblas, dev, oracle, piped):
-    """HEAD/TAIL partial rows go to the carry buffer, the rest to C and every replica."""
+    """HEAD/TAIL partial rows go to the carry buffer, the rest to C and every replica ("bulk": the replica is written
+    by TMA bulk stores of the row slices, SBLAS_FLAG_STITCH_BULK)."""
     import torch
     K = sblas.kernels
     rng = np.random.default_rng(11)
@@ -353,7 +354,7 @@ def test_spmm_rowblock_partials_and_replicas(sblas, dev, oracle, piped):
     plan = K.Plan(drp, len(ci))
     assert plan.build_rowblocks(dci, dv)[1] > 0
     o = sblas.make_opts(variant=sblas.SPMM_ROWBLOCK_PIPE if piped else sblas.SPMM_ROWBLOCK,
-                        flags=sblas.FLAG_HEAD_PARTIAL | sblas.FLAG_TAIL_PARTIAL,
+                        flags=sblas.FLAG_HEAD_PARTIAL | sblas.FLAG_TAIL_PARTIAL | (sblas.FLAG_STITCH_BULK if piped == "bulk" else 0),
                         replicas=[rep.data_ptr()], carry=carry.data_ptr())
     K.spmm(drp, dci, dv, k, sblas.ROW_MAJOR, dB, k, dC, k, 2.0, 0.5, w, plan=plan, opts=o)
     torch.cuda.synchronize()
