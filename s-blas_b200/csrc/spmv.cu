@@ -1186,6 +1186,14 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
     auto_gather = true;
   }
   const bool vec = aligned16(ci) && aligned16(v);
+  // SPLIT reads col_idx / val ONE nnz per lane and load (consecutive lanes = consecutive nnz, coalesced 4-byte loads)
+  // rather than four consecutive nnz per lane by 128-bit loads: the 32 x gathers of one instruction then belong to
+  // 32 CONSECUTIVE nnz — mostly one row, ascending columns — and share x lines where the row is dense (the hub
+  // columns of a power-law matrix), while at stride 4 every gather instruction touches the lines of 128 nnz.  The
+  // L1TEX wavefronts of the gathers are what bounds config 4: 0.632 -> 0.598 ms (profiles/r02_exp_c4_scalar.log).
+  // SBLAS_SPLIT_VEC=1 brings the 128-bit loads back.
+  static const int env_split_vec = [] { const char* e = getenv("SBLAS_SPLIT_VEC"); return e ? atoi(e) : 0; }();
+  const bool vec_split = vec && env_split_vec != 0;
   int rc = 0;
   if (variant == SBLAS_SPMV_COLPANEL) {
     // P passes of the PIPE kernel, one per column panel of the plan's mirror (colpanel.cu): pass p gathers
@@ -1319,13 +1327,13 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
         // warps on tiles that are one slice of a long row, but its search + scan cost more than they did)
         const bool legacy = (flags & SBLAS_FLAG_SPLIT_MERGE) == 0;
         const bool serial = (flags & SBLAS_FLAG_SPLIT_SERIAL) != 0;
-        auto kern = legacy ? (serial ? (vec ? spmv_split_kernel<T, kSpmvBlock, true, false> : spmv_split_kernel<T, kSpmvBlock, false, false>)
+        auto kern = legacy ? (serial ? (vec_split ? spmv_split_kernel<T, kSpmvBlock, true, false> : spmv_split_kernel<T, kSpmvBlock, false, false>)
                                      : (flags & SBLAS_FLAG_NO_L1)
-                                           ? (vec ? spmv_split_kernel<T, kSpmvBlock, true, true, true> : spmv_split_kernel<T, kSpmvBlock, false, true, true>)
-                                           : (vec ? spmv_split_kernel<T, kSpmvBlock, true, true> : spmv_split_kernel<T, kSpmvBlock, false, true>))
-                           : (vec ? spmv_merge_kernel<T, kSpmvBlock, true> : spmv_merge_kernel<T, kSpmvBlock, false>);
+                                           ? (vec_split ? spmv_split_kernel<T, kSpmvBlock, true, true, true> : spmv_split_kernel<T, kSpmvBlock, false, true, true>)
+                                           : (vec_split ? spmv_split_kernel<T, kSpmvBlock, true, true> : spmv_split_kernel<T, kSpmvBlock, false, true>))
+                           : (vec_split ? spmv_merge_kernel<T, kSpmvBlock, true> : spmv_merge_kernel<T, kSpmvBlock, false>);
         if (flags & SBLAS_FLAG_SPLIT_SEG)
-          kern = vec ? spmv_split_seg_kernel<T, kSpmvBlock, true> : spmv_split_seg_kernel<T, kSpmvBlock, false>;
+          kern = vec_split ? spmv_split_seg_kernel<T, kSpmvBlock, true> : spmv_split_seg_kernel<T, kSpmvBlock, false>;
         {  // experiment hook: SBLAS_SPLIT_CARVEOUT=<percent of the 256 KB given to shared memory>; the driver's
            // default takes whatever makes the most CTAs resident, which can leave almost no L1 (tile >= 3072)
           static const int carve = [] { const char* e = getenv("SBLAS_SPLIT_CARVEOUT"); return e ? atoi(e) : -1; }();

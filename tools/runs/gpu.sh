@@ -61,7 +61,9 @@ for step in "$@"; do
       timeout 1500 ncu --set full --clock-control none --import-source on -k "regex:$b" -s 4 -c 2 -f -o gpurun_out/ncu_$a \
         python bench.py $args > gpurun_out/ncu_$a.log 2>&1
       echo "ncu $a exit $?"
-      [ -f gpurun_out/ncu_$a.ncu-rep ] && python tools/ncu_summary.py gpurun_out/ncu_$a.ncu-rep gpurun_out/ncu_${a}_summary.txt ;;
+      [ -f gpurun_out/ncu_$a.ncu-rep ] && python tools/ncu_summary.py gpurun_out/ncu_$a.ncu-rep gpurun_out/ncu_${a}_summary.txt
+      # gpurun brings back at most 64 MiB: keep the summary, drop big reports
+      [ -f gpurun_out/ncu_$a.ncu-rep ] && [ $(stat -c %s gpurun_out/ncu_$a.ncu-rep) -gt 12000000 ] && rm -f gpurun_out/ncu_$a.ncu-rep ;;
     sweep)
       run "$step"
       timeout 1200 python tools/sweep.py --workload $a $b > gpurun_out/sweep_$a.log 2>&1; echo "sweep $a exit $?"; tail -30 gpurun_out/sweep_$a.log ;;
