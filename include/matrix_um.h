@@ -124,6 +124,10 @@ class CsrSparseMatrix {
           memcpy(csrVal_gpu[i], csrVal, get_val_size());
         }
         SBLAS_SAFE_CALL(sblas_plan_create_on((int)i, (int32_t)height, (int64_t)nnz, (const int32_t*)csrRowPtr_gpu[i], &plan_gpu[i]));
+        /* SpMV tile table + column-locality statistic now, and the column-panel mirror for gather-heavy inputs (a device
+           copy owned by the plan; building it touches this replica's managed pages on GPU i) */
+        SBLAS_SAFE_CALL(sblas_plan_prepare_spmv_on((int)i, sizeof(DataType) == 8, plan_gpu[i], (const int32_t*)csrColIdx_gpu[i],
+                                                   csrVal_gpu[i], (int32_t)width));
       }
     } else {
       SAFE_ALOC_HOST(nnz_gpu, n_gpu * sizeof(IdxType));
@@ -144,6 +148,8 @@ class CsrSparseMatrix {
           csrVal_gpu[i] = csrVal + (size_t)i * (size_t)avg_nnz;
           SBLAS_SAFE_CALL(sblas_plan_create_on((int)i, (int32_t)(get_gpu_row_ptr_num(i) - 1), (int64_t)nnz_gpu[i],
                                                (const int32_t*)csrRowPtr_gpu[i], &plan_gpu[i]));
+          SBLAS_SAFE_CALL(sblas_plan_prepare_spmv_on((int)i, sizeof(DataType) == 8, plan_gpu[i], (const int32_t*)csrColIdx_gpu[i],
+                                                     csrVal_gpu[i], (int32_t)width));
         }
         printf("gpu-%d,start-row:%d,stop-row:%d,num-rows:%ld,num-nnz:%d\n", i, (int)starting_row_gpu[i],
                (int)stoping_row_gpu[i], (long)get_gpu_row_ptr_num(i), (int)nnz_gpu[i]);
