@@ -99,6 +99,9 @@ def main():
     plan = K.Plan(rp, nnz)
     if op == "spmm":
         plan.build_rowblocks(ci, v)
+    else:   # what CsrSparseMatrix::sync2gpu does for SpMV: tile table, col_jump, column-panel mirror when it pays
+        plan.prepare(ci, cols, esz)
+        out["colpanels"] = plan.build_colpanels(ci, v, cols)
     xB = pkg.synth.fill_uniform(torch.empty(cols * k, dtype=tdt, device=dev), stream_id=11)
     yC = torch.ones(rows * k, dtype=tdt, device=dev)
     if op == "spmv":
