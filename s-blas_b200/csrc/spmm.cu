@@ -1098,7 +1098,8 @@ static int launch_rm(cudaStream_t st, const TileTable* tt, int G, int NB, const 
       sink.k % VEC == 0 && (sink.ldc * (int64_t)sizeof(T)) % 16 == 0) {
     constexpr int GPB = kSpmmBlock / 32;
     const size_t rowbytes = (size_t)sink.k * sizeof(T);
-    int32_t chunk = (int32_t)((32 * 1024) / rowbytes) / GPB * GPB;
+    static const int env_kb = [] { const char* e = getenv("SBLAS_STITCH_CHUNK_KB"); const int v = e ? atoi(e) : 0; return v > 0 ? std::min(v, 160) : 32; }();
+    int32_t chunk = (int32_t)(((size_t)env_kb * 1024) / rowbytes) / GPB * GPB;
     chunk = std::max(chunk, GPB);
     const size_t smem = (size_t)chunk * rowbytes;
 #define SBLAS_RMB(NN)                                                                                       \

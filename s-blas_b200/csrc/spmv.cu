@@ -1218,6 +1218,7 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
         if ((rc = kernel_residency(kern, kSellSigma, 0, &per_sm, &n_sm)) != 0) break;
         static const int env_g = [] { const char* e = getenv("SBLAS_SELL_GRID"); return e ? atoi(e) : 0; }();   // CTAs per SM (experiments)
         const int grid = std::max(1, std::min(n_win, n_sm * (env_g > 0 ? std::min(env_g, per_sm) : per_sm)));
+        // (forcing 5 / 6 resident CTAs with __launch_bounds__ spills at 48 / 40 registers: 2.97 -> 3.73 / 4.07 ms, dropped)
         if (env_u == 8) spmv_sell_kernel<T, 8><<<grid, kSellSigma, 0, st>>>(sl.n_slices, sl.d_sptr, sl.d_perm, sl.d_col, (const T*)sl.d_val, x, ps);
         else if (env_u == 2) spmv_sell_kernel<T, 2><<<grid, kSellSigma, 0, st>>>(sl.n_slices, sl.d_sptr, sl.d_perm, sl.d_col, (const T*)sl.d_val, x, ps);
         else
