@@ -209,10 +209,13 @@ SBLAS_API int sblas_plan_prepare_i32(void* stream, sblasPlan_t plan, const int32
  * CsrSparseMatrix::sync2gpu next to the CSR arrays of matrix.h:376-387): A split into n_panels column panels,
  * each a CSR of its own that keeps the storage order of every row.  SpMV then runs one pass per panel, pass p
  * gathering only from an L2-resident slice of x, the raw running row sums carried from pass to pass (rows whose
- * columns ascend are still summed in CSR order).  n_panels = 0: automatic — built only when x (cols elements)
- * exceeds 96 MB and the plan's col_jump statistic exceeds cols / 256 (uniform-random columns), with x slices
- * of at most 48 MB (environment SBLAS_COLPANEL_MB); n_panels >= 1 forces that many panels (<= 32).  The mirror holds a
- * COPY of col_idx / val: rebuild it after changing them. */
+ * columns ascend are still summed in CSR order).  n_panels = 0: automatic — x slices of at most 48 MB (environment
+ * SBLAS_COLPANEL_MB) when x (cols elements) exceeds 96 MB and the plan's col_jump statistic exceeds cols / 256
+ * (uniform-random columns); else ONE panel when the matrix has >= 2^20 nnz, no row above 4096 nnz and its sliced-ELL
+ * form pads by < 25 % (the per-lane kernel over coalesced 32-row slices is also the fastest SpMV on regular rows);
+ * nothing for skewed or small inputs, when device memory is short, or with SBLAS_SPMV_MIRROR=0 in the environment.
+ * n_panels >= 1 forces that many panels (<= 32).  The mirror holds a COPY of col_idx / val: rebuild it after
+ * changing them. */
 SBLAS_API int sblas_plan_build_colpanels_f64(void* stream, sblasPlan_t plan, const int32_t* d_colidx,
                                              const double* d_val, int32_t cols, int32_t n_panels);
 SBLAS_API int sblas_plan_build_colpanels_f32(void* stream, sblasPlan_t plan, const int32_t* d_colidx,

@@ -17,8 +17,10 @@
 // applies alpha and beta.  Extra traffic: P x (row pointers + carried sums read and written) =
 // P x 20 B per row, i.e. +19 % on the compulsory bytes at P = 4.
 //
-// Only built when it pays (sblas_plan_build_colpanels_*, n_panels = 0): x larger than 96 MB and the
-// plan's column-locality statistic says consecutive rows are far apart (col_jump > cols / 256).
+// Built automatically (sblas_plan_build_colpanels_*, n_panels = 0) in two cases: gather-heavy inputs (x larger than
+// 96 MB and the plan's column-locality statistic says consecutive rows are far apart, col_jump > cols / 256) get
+// P >= 2 panels; every other input of >= 1M nnz whose rows fit the sliced-ELL form gets ONE panel, because the
+// barrier-free per-lane kernel over coalesced slices also beats the staged kernel on regular rows (see below).
 #include <cub/cub.cuh>
 
 #include "plan.cuh"
@@ -151,23 +153,59 @@ void colpanels_free(sblasPlan_st* plan) {
 }
 
 template <typename T>
+static int build_colpanels_n(cudaStream_t st, sblasPlan_st* plan, const int32_t* ci, const T* val, int32_t cols, int P,
+                             bool auto_mode);
+
+// rows of a matrix worth a mirror in automatic mode (smaller inputs are launch-bound whatever the kernel)
+constexpr int64_t kAutoMirrorMinNnz = 1 << 20;
+
+template <typename T>
 static int build_colpanels(cudaStream_t st, sblasPlan_st* plan, const int32_t* ci, const T* val, int32_t cols,
                            int32_t n_panels) {
   SBLAS_CHECK(plan && ci && val && cols > 0, "plan_build_colpanels: bad arguments");
   colpanels_free(plan);
   const int32_t rows = plan->rows;
   if (rows == 0 || plan->nnz == 0) return 0;
-  int P = n_panels;
-  if (P == 0) {
-    // automatic: only for gather-heavy inputs, x slices of SBLAS_COLPANEL_MB (default 48) MB: on the 16M x 32
-    // uniform-random input 3 panels (43 MB) run 2.83 ms, 2 (64 MB) 2.98, 4 (32 MB) 2.91, 6 3.21, 8 3.48
-    // (profiles/r02_exp_colpanel_v4_sell.log): fewer passes carry the row sums less often, but the slice must
-    // stay L2-resident beside the streaming panel
-    if (!measure_gather_heavy(st, plan, plan->d_rowptr, ci, rows, cols, sizeof(T))) return 0;
+  if (n_panels != 0) return build_colpanels_n<T>(st, plan, ci, val, cols, n_panels, false);
+  // ---- automatic (what sync2gpu asks for).  SBLAS_SPMV_MIRROR=0 forbids any mirror.
+  {
+    const char* em = getenv("SBLAS_SPMV_MIRROR");
+    if (em && atoi(em) == 0) return 0;
+  }
+  int P;
+  if (measure_gather_heavy(st, plan, plan->d_rowptr, ci, rows, cols, sizeof(T))) {
+    // gather-heavy inputs: x slices of SBLAS_COLPANEL_MB (default 48) MB: on the 16M x 32 uniform-random input 3
+    // panels (43 MB) run 2.83 ms, 2 (64 MB) 2.98, 4 (32 MB) 2.91, 6 3.21, 8 3.48 (profiles/r02_exp_colpanel_v4_sell.log):
+    // fewer passes carry the row sums less often, but the slice must stay L2-resident beside the streaming panel
     static const int mb = [] { const char* e = getenv("SBLAS_COLPANEL_MB"); const int v = e ? atoi(e) : 0; return v > 0 ? v : 48; }();
     P = (int)ceil_div((int64_t)cols * (int64_t)sizeof(T), (int64_t)mb << 20);
-    if (P < 2) return 0;
+    if (P < 2) P = 1;
+  } else {
+    // every other input of some size whose rows fit the sliced-ELL form (padding < 25 %): ONE panel.  The per-lane
+    // walk over coalesced slices needs no staging, no barrier and no shared memory, and measured faster than the
+    // TMA-staged PIPE kernel on regular rows: banded 16M x 32 1.33-1.46 -> 1.08 ms (98 % of the measured HBM copy
+    // rate), 2-D Laplacian 76.1 -> 73.2 us (profiles/r02_exp_sell_single_panel.log); still one lane per row in storage
+    // order, i.e. bit-identical to spmv.h:24-30.  Skewed inputs (R-MAT) fail the padding test and keep SPLIT.
+    P = 1;
   }
+  if (P == 1 && (plan->nnz < kAutoMirrorMinNnz || plan->max_row_nnz > 4096)) return 0;
+  {  // room for the mirror and its transient CSR copy? (a mirror is an optimisation: never fail sync2gpu for it)
+    size_t free_b = 0, total_b = 0;
+    const size_t need = (size_t)plan->nnz * (sizeof(T) + 4) * 5 / 2 + (size_t)rows * 32;
+    if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess || free_b < need + (1ull << 30)) { cudaGetLastError(); return 0; }
+  }
+  if (build_colpanels_n<T>(st, plan, ci, val, cols, P, true) != 0) {
+    colpanels_free(plan);
+    cudaGetLastError();
+    return 0;
+  }
+  return 0;
+}
+
+template <typename T>
+static int build_colpanels_n(cudaStream_t st, sblasPlan_st* plan, const int32_t* ci, const T* val, int32_t cols, int P,
+                             bool auto_mode) {
+  const int32_t rows = plan->rows;
   SBLAS_CHECK(P >= 1 && P <= kCpMaxPanels, "plan_build_colpanels: 1..%d panels", kCpMaxPanels);
   const int32_t W = (int32_t)((ceil_div(cols, P) + 31) & ~(int64_t)31);
   ColPanels& cp = plan->cp;
@@ -269,6 +307,8 @@ static int build_colpanels(cudaStream_t st, sblasPlan_st* plan, const int32_t* c
       cp.sell.clear();
     }
   }
+  // automatic single panel without the sliced-ELL form = a plain copy of the CSR arrays: pointless, drop it
+  if (auto_mode && P == 1 && cp.sell.empty()) colpanels_free(plan);
   return 0;
 }
 

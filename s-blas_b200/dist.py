@@ -144,6 +144,10 @@ class RowSplitOp:
         self.plan = plan if plan is not None else (K.Plan(rp, val.numel()) if self.r1 > self.r0 else None)
         if plan is None and self.plan is not None and not (k == 1 and ld == 1):
             self.plan.build_rowblocks(ci, val)      # SpMM: row-block mirror when it pays (sync2gpu work)
+        elif plan is None and self.plan is not None:
+            # SpMV: tile table + column statistic now (no call then synchronises), sliced-ELL mirror when it pays
+            self.plan.prepare(ci, cols, val.element_size())
+            self.plan.build_colpanels(ci, val, cols)
         self.stitch = stitch if self.world > 1 else "none"
         self.equal = len({self.row_begin[i + 1] - self.row_begin[i] for i in range(self.world)}) == 1
         self.opts = make_opts(flags=flags) if flags else None   # extra SBLAS_FLAG_* for the kernels (experiments)

@@ -56,9 +56,15 @@ def _spmv_case(sblas, dev, oracle, gen, dtype, n_win, expect=None):
     assert float(((y - y2).abs() / bnd).max()) <= 2 * TOL[dtype]
 
 
-def test_c2_full_size(sblas, dev, oracle):
-    """configs[1]: 2-D Laplacian, 4M rows, fp64 SpMV, AUTO (staged PIPE kernel, strided tile order)."""
-    _spmv_case(sblas, dev, oracle, lambda td: sblas.synth.laplace2d(2048, 2048, td, dev), "f64", 20000)
+@pytest.mark.parametrize("mirror", ["1", "0"])
+def test_c2_full_size(sblas, dev, oracle, mirror, monkeypatch):
+    """configs[1]: 2-D Laplacian, 4M rows, fp64 SpMV, AUTO: the single sliced-ELL panel sync2gpu keeps for regular
+    rows (4 % padding: boundary rows have 3-4 nnz), and without mirrors the staged PIPE kernel, strided tile order."""
+    monkeypatch.setenv("SBLAS_SPMV_MIRROR", mirror)
+
+    def expect(plan, panels):
+        assert panels == ((1, 1 << 22) if mirror == "1" else (0, 0)), panels
+    _spmv_case(sblas, dev, oracle, lambda td: sblas.synth.laplace2d(2048, 2048, td, dev), "f64", 20000, expect)
 
 
 def test_c4_full_size(sblas, dev, oracle):
@@ -78,9 +84,21 @@ def test_c3v_full_size_column_panels(sblas, dev, oracle):
     _spmv_case(sblas, dev, oracle, lambda td: sblas.synth.uniform(1 << 24, 1 << 24, 32, td, dev), "f64", 4096, expect)
 
 
-def test_b32_full_size_consecutive_tiles(sblas, dev, oracle):
-    """banded 16M x 32, fp64: x larger than L2 but local rows (col_jump ~ 1) -> no mirror, the staged kernel with
-    CONSECUTIVE tiles per CTA (spmv.cu launch_pipe: rows * col_jump * 8 B > 96 MB)."""
+def test_b32_full_size_single_panel_sell(sblas, dev, oracle):
+    """banded 16M x 32, fp64: local rows (col_jump ~ 1), regular row lengths -> sync2gpu keeps ONE sliced-ELL panel and
+    AUTO runs the per-lane kernel on it (no padding: every row has 32 nnz)."""
+    def expect(plan, panels):
+        assert 0.0 <= plan.col_jump() < 4.0 and panels == (1, 1 << 24)
+        is_sell, stored = plan.colpanel_format()
+        assert is_sell and stored == (1 << 29)
+    _spmv_case(sblas, dev, oracle, lambda td: sblas.synth.banded(1 << 24, 32, td, dev), "f64", 4096, expect)
+
+
+def test_b32_full_size_consecutive_tiles(sblas, dev, oracle, monkeypatch):
+    """the same input without any mirror (SBLAS_SPMV_MIRROR=0): x larger than L2 but local rows -> the staged PIPE
+    kernel with CONSECUTIVE tiles per CTA (spmv.cu launch_pipe: rows * col_jump * 8 B > 96 MB)."""
+    monkeypatch.setenv("SBLAS_SPMV_MIRROR", "0")
+
     def expect(plan, panels):
         assert 0.0 <= plan.col_jump() < 4.0 and panels == (0, 0)
     _spmv_case(sblas, dev, oracle, lambda td: sblas.synth.banded(1 << 24, 32, td, dev), "f64", 4096, expect)
