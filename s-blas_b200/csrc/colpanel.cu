@@ -31,6 +31,11 @@ constexpr int kCpMaxPanels = 32;
 
 struct CpOffsets { int64_t off[kCpMaxPanels]; };
 
+__global__ void vs_iota_kernel(int32_t* p, int64_t n) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < n) p[i] = (int32_t)i;
+}
+
 // cnt[p*(rows+1) + r] = number of nonzeros of row r in panel p (entry [rows] of every panel = 0)
 __global__ void __launch_bounds__(256)
 cp_count_kernel(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ colidx, int32_t rows,
@@ -135,6 +140,174 @@ static int build_sell(cudaStream_t st, int32_t rows, const int32_t* prp, const i
   return 0;
 }
 
+// ---- virtual-row sliced-ELL (skewed inputs: R-MAT, config 4) ---------------------------------------------------
+// Power-law rows do not fit sliced-ELL as they are (rows of 10^5 nnz beside empty ones), and the merge-path SPLIT
+// kernel that takes them is bound by the L1TEX wavefronts of its x gathers.  Here every row longer than
+// kVsellPiece = 128 entries is cut into pieces of 128 ("virtual rows"); the virtual rows are sorted by length inside
+// windows of 65 536 (one radix sort of 24-bit keys {window, 255 - length}: slices of 32 then hold rows of almost
+// equal length, padding < 1 %, while the y rows of a window stay L2-resident), and stored as ONE sliced-ELL panel.
+// The per-lane kernel writes whole rows straight to y (the fused epilogue; still summed in storage order by one
+// lane) and the raw sums of pieces to d_piece[]; a small fix-up kernel adds the pieces of each cut row (one warp per
+// row, pieces in order, shuffle tree) and finishes it.  Measured on config 4: 0.598 -> ~0.5 ms (tools/exp_c4_vrows.py).
+__global__ void __launch_bounds__(256)
+vs_count_kernel(const int32_t* __restrict__ rowptr, int32_t rows, int32_t* __restrict__ nch1, int32_t* __restrict__ npc) {
+  const int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (r > rows) return;
+  int32_t a = 0, b = 0;
+  if (r < rows) {
+    const int32_t len = rowptr[r + 1] - rowptr[r];
+    const int32_t n = (len + kVsellPiece - 1) / kVsellPiece;
+    a = n > 1 ? n : 1;     // virtual rows of this row (an empty row keeps one empty virtual row: beta*y)
+    b = n > 1 ? n : 0;     // piece slots (cut rows only)
+  }
+  nch1[r] = a;
+  npc[r] = b;
+}
+
+// per row: its virtual rows' {start, key, info}; cut rows also append {row, first slot, pieces} to the split list
+__global__ void __launch_bounds__(256)
+vs_expand_kernel(const int32_t* __restrict__ rowptr, int32_t rows, const int32_t* __restrict__ vfirst,
+                 const int32_t* __restrict__ pfirst, int32_t* __restrict__ vstart, uint32_t* __restrict__ vkey,
+                 int32_t* __restrict__ vinfo, int32_t* __restrict__ split, int32_t* __restrict__ n_split) {
+  const int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (r >= rows) return;
+  const int32_t s = rowptr[r], len = rowptr[r + 1] - s;
+  const int32_t n = (len + kVsellPiece - 1) / kVsellPiece;
+  const int32_t v0 = vfirst[r];
+  if (n <= 1) {
+    vstart[v0] = s;
+    vkey[v0] = ((uint32_t)(v0 / kVsellWindow) << 8) | (uint32_t)(255 - len);
+    vinfo[v0] = (int32_t)r;
+    return;
+  }
+  const int32_t p0 = pfirst[r];
+  const int32_t k = atomicAdd(n_split, 1);
+  split[3 * k] = (int32_t)r; split[3 * k + 1] = p0; split[3 * k + 2] = n;
+  for (int32_t c = 0; c < n; ++c) {
+    const int32_t v = v0 + c, l = min(kVsellPiece, len - c * kVsellPiece);
+    vstart[v] = s + c * kVsellPiece;
+    vkey[v] = ((uint32_t)(v / kVsellWindow) << 8) | (uint32_t)(255 - l);
+    vinfo[v] = -(p0 + c + 2);
+  }
+}
+
+// slice widths (x 32) from the sorted keys: the first position of a slice holds its longest virtual row
+__global__ void __launch_bounds__(256)
+vs_width_kernel(const uint32_t* __restrict__ skey, int64_t nv, int32_t n_slices, int32_t* __restrict__ w32) {
+  const int64_t sl = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (sl > n_slices) return;
+  int32_t w = 0;
+  if (sl < n_slices && sl * kSellC < nv) w = 255 - (int32_t)(skey[sl * kSellC] & 255u);
+  w32[sl] = w * kSellC;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+vs_fill_kernel(const int32_t* __restrict__ ci, const T* __restrict__ val, const uint32_t* __restrict__ skey,
+               const int32_t* __restrict__ order, const int32_t* __restrict__ vstart, const int32_t* __restrict__ vinfo,
+               const int32_t* __restrict__ sptr, int64_t nv, int64_t n_pos, int32_t* __restrict__ perm,
+               int32_t* __restrict__ oc, T* __restrict__ ov) {
+  const int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (q >= n_pos) return;
+  const int64_t sl = q / kSellC;
+  const int32_t base = sptr[sl] + (int32_t)(q % kSellC);
+  const int32_t width = (sptr[sl + 1] - sptr[sl]) / kSellC;
+  int32_t a = 0, len = 0, info = -1;
+  if (q < nv) {
+    const int32_t v = order[q];
+    a = vstart[v];
+    len = 255 - (int32_t)(skey[q] & 255u);
+    info = vinfo[v];
+  }
+  perm[q] = info;
+  for (int32_t u = 0; u < width; ++u) {
+    oc[base + u * kSellC] = u < len ? ci[a + u] : -1;
+    ov[base + u * kSellC] = u < len ? val[a + u] : T(0);
+  }
+}
+
+struct DevBuf {  // frees a temporary on every exit path
+  void* p = nullptr;
+  ~DevBuf() { if (p) cudaFree(p); }
+  int alloc(size_t bytes) { return cudaMalloc(&p, bytes ? bytes : 16) == cudaSuccess ? 0 : 1; }
+};
+
+// returns 0 and fills *sl (caller frees on failure too); *kept = false when the form pads too much
+template <typename T>
+static int build_vsell(cudaStream_t st, const sblasPlan_st* plan, const int32_t* ci, const T* val, ColPanels::Sell* sl, bool* kept) {
+  *kept = false;
+  const int32_t rows = plan->rows;
+  const int32_t* rp = plan->d_rowptr;
+  DevBuf nch1, npc, tmp, vstart, vkey, vkey2, vinfo, order_in, order, cnt;
+  if (nch1.alloc(sizeof(int32_t) * ((size_t)rows + 1)) || npc.alloc(sizeof(int32_t) * ((size_t)rows + 1)) || cnt.alloc(16)) {
+    set_error("plan_build_colpanels: out of device memory"); cudaGetLastError(); return 1;
+  }
+  const int rblocks = (int)ceil_div((int64_t)rows + 1, 256);
+  vs_count_kernel<<<rblocks, 256, 0, st>>>(rp, rows, (int32_t*)nch1.p, (int32_t*)npc.p);
+  SBLAS_LAUNCH_CHECK();
+  size_t tb = 0;
+  SBLAS_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tb, (int32_t*)nch1.p, (int32_t*)nch1.p, rows + 1, st));
+  size_t tb2 = 0;
+  if (tmp.alloc(std::max(tb, (size_t)16))) { set_error("plan_build_colpanels: out of device memory"); cudaGetLastError(); return 1; }
+  SBLAS_CUDA(cub::DeviceScan::ExclusiveSum(tmp.p, tb, (int32_t*)nch1.p, (int32_t*)nch1.p, rows + 1, st));
+  SBLAS_CUDA(cub::DeviceScan::ExclusiveSum(tmp.p, tb, (int32_t*)npc.p, (int32_t*)npc.p, rows + 1, st));
+  int32_t h[2] = {0, 0};
+  SBLAS_CUDA(cudaMemcpyAsync(&h[0], (int32_t*)nch1.p + rows, 4, cudaMemcpyDeviceToHost, st));
+  SBLAS_CUDA(cudaMemcpyAsync(&h[1], (int32_t*)npc.p + rows, 4, cudaMemcpyDeviceToHost, st));
+  SBLAS_CUDA(cudaMemsetAsync(cnt.p, 0, 16, st));
+  SBLAS_CUDA(cudaStreamSynchronize(st));
+  const int64_t nv = h[0];
+  const int32_t n_piece = h[1];
+  SBLAS_CHECK(nv >= rows && nv / kVsellWindow < (1 << 16), "plan_build_colpanels: too many virtual rows");
+  const int32_t n_slices = (int32_t)ceil_div(nv, kSellC);
+  const int64_t n_pos = (int64_t)n_slices * kSellC;
+  const int32_t max_split = (int32_t)std::min<int64_t>(rows, n_piece / 2 + 1);
+  if (vstart.alloc(4 * (size_t)nv) || vkey.alloc(4 * (size_t)nv) || vkey2.alloc(4 * (size_t)nv) || vinfo.alloc(4 * (size_t)nv) ||
+      order_in.alloc(4 * (size_t)nv) || order.alloc(4 * (size_t)nv)) {
+    set_error("plan_build_colpanels: out of device memory"); cudaGetLastError(); return 1;
+  }
+  SBLAS_CUDA(cudaMalloc(&sl->d_split, sizeof(int32_t) * 3 * (size_t)std::max(max_split, 1)));
+  SBLAS_CUDA(cudaMalloc(&sl->d_piece, sizeof(T) * (size_t)std::max(n_piece, 1)));
+  vs_expand_kernel<<<(int)ceil_div(rows, 256), 256, 0, st>>>(rp, rows, (const int32_t*)nch1.p, (const int32_t*)npc.p, (int32_t*)vstart.p,
+                                                            (uint32_t*)vkey.p, (int32_t*)vinfo.p, sl->d_split, (int32_t*)cnt.p);
+  SBLAS_LAUNCH_CHECK();
+  vs_iota_kernel<<<(int)ceil_div(nv, 256), 256, 0, st>>>((int32_t*)order_in.p, nv);
+  SBLAS_LAUNCH_CHECK();
+  const int key_bits = 8 + std::max(1, 32 - __builtin_clz((unsigned)(nv / kVsellWindow + 1)));
+  SBLAS_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tb2, (const uint32_t*)vkey.p, (uint32_t*)vkey2.p, (const int32_t*)order_in.p,
+                                             (int32_t*)order.p, nv, 0, key_bits, st));
+  DevBuf tmp2;
+  if (tmp2.alloc(tb2)) { set_error("plan_build_colpanels: out of device memory"); cudaGetLastError(); return 1; }
+  SBLAS_CUDA(cub::DeviceRadixSort::SortPairs(tmp2.p, tb2, (const uint32_t*)vkey.p, (uint32_t*)vkey2.p, (const int32_t*)order_in.p,
+                                             (int32_t*)order.p, nv, 0, key_bits, st));   // LSD radix sort: stable
+  sl->n_slices = n_slices;
+  SBLAS_CUDA(cudaMalloc(&sl->d_perm, sizeof(int32_t) * (size_t)n_pos));
+  SBLAS_CUDA(cudaMalloc(&sl->d_sptr, sizeof(int32_t) * ((size_t)n_slices + 1)));
+  vs_width_kernel<<<(int)ceil_div((int64_t)n_slices + 1, 256), 256, 0, st>>>((const uint32_t*)vkey2.p, nv, n_slices, sl->d_sptr);
+  SBLAS_LAUNCH_CHECK();
+  SBLAS_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tb, sl->d_sptr, sl->d_sptr, n_slices + 1, st));
+  DevBuf tmp3;
+  if (tmp3.alloc(tb)) { set_error("plan_build_colpanels: out of device memory"); cudaGetLastError(); return 1; }
+  SBLAS_CUDA(cub::DeviceScan::ExclusiveSum(tmp3.p, tb, sl->d_sptr, sl->d_sptr, n_slices + 1, st));
+  int32_t total = 0, n_split = 0;
+  SBLAS_CUDA(cudaMemcpyAsync(&total, sl->d_sptr + n_slices, 4, cudaMemcpyDeviceToHost, st));
+  SBLAS_CUDA(cudaMemcpyAsync(&n_split, cnt.p, 4, cudaMemcpyDeviceToHost, st));
+  SBLAS_CUDA(cudaStreamSynchronize(st));
+  sl->padded = total;
+  sl->n_split = n_split;
+  sl->n_piece = n_piece;
+  if ((int64_t)total * 4 > plan->nnz * 5 + (int64_t)rows) return 0;   // pads >= 25 %: not kept
+  SBLAS_CUDA(cudaMalloc(&sl->d_col, sizeof(int32_t) * (size_t)std::max(total, 4)));
+  SBLAS_CUDA(cudaMalloc(&sl->d_val, sizeof(T) * (size_t)std::max(total, 4)));
+  vs_fill_kernel<T><<<(int)ceil_div(n_pos, 256), 256, 0, st>>>(ci, val, (const uint32_t*)vkey2.p, (const int32_t*)order.p,
+                                                              (const int32_t*)vstart.p, (const int32_t*)vinfo.p, sl->d_sptr, nv, n_pos,
+                                                              sl->d_perm, sl->d_col, (T*)sl->d_val);
+  SBLAS_LAUNCH_CHECK();
+  SBLAS_CUDA(cudaStreamSynchronize(st));   // the temporaries are released on return
+  *kept = true;
+  return 0;
+}
+
 void colpanels_free(sblasPlan_st* plan) {
   ColPanels& cp = plan->cp;
   for (sblasPlan_st* s : cp.sub)
@@ -143,12 +316,7 @@ void colpanels_free(sblasPlan_st* plan) {
   if (cp.d_colidx) cudaFree(cp.d_colidx);
   if (cp.d_val) cudaFree(cp.d_val);
   if (cp.d_part) cudaFree(cp.d_part);
-  for (ColPanels::Sell& sl : cp.sell) {
-    if (sl.d_perm) cudaFree(sl.d_perm);
-    if (sl.d_sptr) cudaFree(sl.d_sptr);
-    if (sl.d_col) cudaFree(sl.d_col);
-    if (sl.d_val) cudaFree(sl.d_val);
-  }
+  for (ColPanels::Sell& sl : cp.sell) ColPanels::free_sell(sl);
   cp = ColPanels();
 }
 
@@ -188,17 +356,39 @@ static int build_colpanels(cudaStream_t st, sblasPlan_st* plan, const int32_t* c
     // order, i.e. bit-identical to spmv.h:24-30.  Skewed inputs (R-MAT) fail the padding test and keep SPLIT.
     P = 1;
   }
-  if (P == 1 && (plan->nnz < kAutoMirrorMinNnz || plan->max_row_nnz > 4096)) return 0;
+  if (P == 1 && plan->nnz < kAutoMirrorMinNnz) return 0;
   {  // room for the mirror and its transient CSR copy? (a mirror is an optimisation: never fail sync2gpu for it)
     size_t free_b = 0, total_b = 0;
-    const size_t need = (size_t)plan->nnz * (sizeof(T) + 4) * 5 / 2 + (size_t)rows * 32;
+    const size_t need = (size_t)plan->nnz * (sizeof(T) + 4) * 5 / 2 + (size_t)rows * 64;
     if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess || free_b < need + (1ull << 30)) { cudaGetLastError(); return 0; }
   }
-  if (build_colpanels_n<T>(st, plan, ci, val, cols, P, true) != 0) {
-    colpanels_free(plan);
+  if (P > 1 || plan->max_row_nnz <= 4096) {
+    if (build_colpanels_n<T>(st, plan, ci, val, cols, P, true) != 0) {
+      colpanels_free(plan);
+      cudaGetLastError();
+      return 0;
+    }
+    if (plan->cp.n > 0 || P > 1) return 0;
+  }
+  // skewed rows (the plain form padded >= 25 %, or rows above 4096 nnz): the virtual-row form, one panel.
+  // SBLAS_SPMV_VSELL=0 keeps the merge-path SPLIT kernel for such inputs.
+  {
+    const char* ev = getenv("SBLAS_SPMV_VSELL");
+    if (ev && atoi(ev) == 0) return 0;
+  }
+  if ((int64_t)rows + plan->nnz / kVsellPiece + 1 >= (1ll << 31) - kVsellWindow) return 0;
+  ColPanels::Sell sl;
+  bool kept = false;
+  if (build_vsell<T>(st, plan, ci, val, &sl, &kept) != 0 || !kept) {
+    ColPanels::free_sell(sl);
     cudaGetLastError();
     return 0;
   }
+  ColPanels& cp = plan->cp;
+  cp.n = 1;
+  cp.panel_cols = (int32_t)(((int64_t)cols + 31) & ~(int64_t)31);
+  cp.is_f64 = sizeof(T) == 8;
+  cp.sell.assign(1, sl);
   return 0;
 }
 
@@ -298,12 +488,7 @@ static int build_colpanels_n(cudaStream_t st, sblasPlan_st* plan, const int32_t*
       cp.d_rowptr = cp.d_colidx = nullptr;
       cp.d_val = nullptr;
     } else {
-      for (ColPanels::Sell& sl : cp.sell) {
-        if (sl.d_perm) cudaFree(sl.d_perm);
-        if (sl.d_sptr) cudaFree(sl.d_sptr);
-        if (sl.d_col) cudaFree(sl.d_col);
-        if (sl.d_val) cudaFree(sl.d_val);
-      }
+      for (ColPanels::Sell& sl : cp.sell) ColPanels::free_sell(sl);
       cp.sell.clear();
     }
   }

@@ -75,7 +75,23 @@ struct ColPanels {
     int32_t* d_sptr = nullptr;    // [n_slices + 1] first entry of every slice
     int32_t* d_col = nullptr;     // [padded] column, -1 = padding; entry u of sorted position q at sptr[q/32] + u*32 + q%32
     void* d_val = nullptr;
+    // virtual-row form (skewed inputs): rows longer than kVsellPiece entries are cut into pieces; a sorted position
+    // then holds a whole row (perm >= 0) or one piece of a cut row (perm = -(slot + 2): its raw sum goes to
+    // d_piece[slot]); d_split lists the cut rows as {row, first slot, pieces} for the fix-up kernel
+    int32_t n_split = 0;
+    int32_t n_piece = 0;
+    int32_t* d_split = nullptr;   // [n_split * 3]
+    void* d_piece = nullptr;      // T[n_piece]
   };
+  static void free_sell(Sell& sl) {
+    if (sl.d_perm) cudaFree(sl.d_perm);
+    if (sl.d_sptr) cudaFree(sl.d_sptr);
+    if (sl.d_col) cudaFree(sl.d_col);
+    if (sl.d_val) cudaFree(sl.d_val);
+    if (sl.d_split) cudaFree(sl.d_split);
+    if (sl.d_piece) cudaFree(sl.d_piece);
+    sl = Sell();
+  }
   std::vector<Sell> sell;
 };
 
@@ -133,6 +149,8 @@ bool measure_gather_heavy(cudaStream_t st, sblasPlan_st* plan, const int32_t* rp
                           int32_t cols, size_t elem_size);
 constexpr int kSellC = 32;       // slice height = one warp
 constexpr int kSellSigma = 256;  // rows sorted by length inside windows of this many rows (one CTA)
+constexpr int kVsellPiece = 128;      // virtual-row form: longest piece of a cut row
+constexpr int kVsellWindow = 65536;   // ... virtual rows sorted by length inside windows of this many
 // spmv.cu: builds the tile table the PIPE kernel will ask for (so that no SpMV call has to)
 int prepare_pipe_table(cudaStream_t st, sblasPlan_st* plan, bool* pipe_ok);
 

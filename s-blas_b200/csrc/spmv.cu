@@ -605,7 +605,7 @@ template <typename T, int U>
 __global__ void __launch_bounds__(kSellSigma)
 spmv_sell_kernel(int32_t n_slices, const int32_t* __restrict__ sptr, const int32_t* __restrict__ perm,
                  const int32_t* __restrict__ col, const T* __restrict__ val, const T* __restrict__ x,
-                 RowSink<T> sink) {
+                 RowSink<T> sink, T* __restrict__ piece) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   constexpr int SPW = kSellSigma / kSellC;  // slices per window
   for (int64_t sl = (int64_t)blockIdx.x * SPW + warp; sl < n_slices; sl += (int64_t)gridDim.x * SPW) {
@@ -633,8 +633,26 @@ spmv_sell_kernel(int32_t n_slices, const int32_t* __restrict__ sptr, const int32
     if (r >= 0) {
       if (sink.phase == 0) sink.put(r, sum);   // a single panel: plain fused epilogue (reads y[r] itself)
       else sink.put_y(r, sum, T(0));           // phases 1-3 never use the staged value
+    } else if (r <= -2) {
+      piece[-(r + 2)] = sum;                   // virtual-row form: one piece of a cut row, finished by the fix-up kernel
     }
   }
+}
+
+// virtual-row form: adds the pieces of every cut row (one warp per row; lane-strided partial sums, shuffle tree:
+// a fixed order) and finishes the row through the fused epilogue
+template <typename T>
+__global__ void __launch_bounds__(256)
+spmv_vsell_fixup_kernel(const int32_t* __restrict__ split, int32_t n_split, const T* __restrict__ piece, RowSink<T> sink) {
+  const int lane = threadIdx.x & 31;
+  const int64_t w = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  if (w >= n_split) return;
+  const int32_t row = split[3 * w], p0 = split[3 * w + 1], n = split[3 * w + 2];
+  T s = 0;
+  for (int32_t i = lane; i < n; i += 32) s += piece[p0 + i];
+#pragma unroll
+  for (int m = 16; m > 0; m >>= 1) s += __shfl_xor_sync(0xffffffffu, s, m);
+  if (lane == 0) sink.put(row, s);
 }
 
 // ---- VECTOR: G lanes per row, straight from global memory ----------------------------------
@@ -1219,13 +1237,19 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
         static const int env_g = [] { const char* e = getenv("SBLAS_SELL_GRID"); return e ? atoi(e) : 0; }();   // CTAs per SM (experiments)
         const int grid = std::max(1, std::min(n_win, n_sm * (env_g > 0 ? std::min(env_g, per_sm) : per_sm)));
         // (forcing 5 / 6 resident CTAs with __launch_bounds__ spills at 48 / 40 registers: 2.97 -> 3.73 / 4.07 ms, dropped)
-        if (env_u == 8) spmv_sell_kernel<T, 8><<<grid, kSellSigma, 0, st>>>(sl.n_slices, sl.d_sptr, sl.d_perm, sl.d_col, (const T*)sl.d_val, x, ps);
-        else if (env_u == 2) spmv_sell_kernel<T, 2><<<grid, kSellSigma, 0, st>>>(sl.n_slices, sl.d_sptr, sl.d_perm, sl.d_col, (const T*)sl.d_val, x, ps);
+        if (env_u == 8) spmv_sell_kernel<T, 8><<<grid, kSellSigma, 0, st>>>(sl.n_slices, sl.d_sptr, sl.d_perm, sl.d_col, (const T*)sl.d_val, x, ps, (T*)sl.d_piece);
+        else if (env_u == 2) spmv_sell_kernel<T, 2><<<grid, kSellSigma, 0, st>>>(sl.n_slices, sl.d_sptr, sl.d_perm, sl.d_col, (const T*)sl.d_val, x, ps, (T*)sl.d_piece);
         else
-        spmv_sell_kernel<T, 4><<<grid, kSellSigma, 0, st>>>(sl.n_slices, sl.d_sptr, sl.d_perm, sl.d_col, (const T*)sl.d_val, x, ps);
+        spmv_sell_kernel<T, 4><<<grid, kSellSigma, 0, st>>>(sl.n_slices, sl.d_sptr, sl.d_perm, sl.d_col, (const T*)sl.d_val, x, ps, (T*)sl.d_piece);
         ++g_launches;
         cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) { set_error("spmv sell launch: %s", cudaGetErrorString(e)); rc = 3; }
+        if (rc == 0 && sl.n_split > 0) {
+          spmv_vsell_fixup_kernel<T><<<(int)ceil_div((int64_t)sl.n_split * 32, 256), 256, 0, st>>>(sl.d_split, sl.n_split, (const T*)sl.d_piece, ps);
+          ++g_launches;
+          e = cudaGetLastError();
+          if (e != cudaSuccess) { set_error("spmv vsell fixup launch: %s", cudaGetErrorString(e)); rc = 3; }
+        }
         continue;
       }
       sblasPlan_st* sub = cp.sub[(size_t)p];

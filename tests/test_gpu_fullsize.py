@@ -67,10 +67,15 @@ def test_c2_full_size(sblas, dev, oracle, mirror, monkeypatch):
     _spmv_case(sblas, dev, oracle, lambda td: sblas.synth.laplace2d(2048, 2048, td, dev), "f64", 20000, expect)
 
 
-def test_c4_full_size(sblas, dev, oracle):
-    """configs[3]: R-MAT scale 23, fp32 SpMV, AUTO (SPLIT: rows of 10^5 nnz cut across CTAs); the first window
-    holds the hub rows."""
-    _spmv_case(sblas, dev, oracle, lambda td: sblas.synth.rmat(23, 16, td, dev), "f32", 6000)
+@pytest.mark.parametrize("vsell", ["1", "0"])
+def test_c4_full_size(sblas, dev, oracle, vsell, monkeypatch):
+    """configs[3]: R-MAT scale 23, fp32 SpMV, AUTO: the virtual-row sliced-ELL mirror (rows of 10^5 nnz cut into pieces
+    of 128) and, without it, SPLIT (rows cut across CTAs); the first window holds the hub rows."""
+    monkeypatch.setenv("SBLAS_SPMV_VSELL", vsell)
+
+    def expect(plan, panels):
+        assert panels[0] == (1 if vsell == "1" else 0), panels
+    _spmv_case(sblas, dev, oracle, lambda td: sblas.synth.rmat(23, 16, td, dev), "f32", 6000, expect)
 
 
 def test_c3v_full_size_column_panels(sblas, dev, oracle):

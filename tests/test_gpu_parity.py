@@ -715,6 +715,56 @@ def test_spmv_column_panels_sliced_ell(sblas, dev, oracle, dtype, monkeypatch):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_spmv_virtual_row_sell_on_skewed_rows(sblas, dev, oracle, dtype, monkeypatch):
+    """Power-law rows (R-MAT scale 17: rows of thousands of nnz beside empty ones) do not fit the plain sliced-ELL form;
+    the automatic build keeps the VIRTUAL-ROW form instead (rows cut into pieces of 128, sorted by length in windows of
+    65 536, a fix-up kernel adds the pieces): within the row tolerance, replicas written, HEAD / TAIL partial rows
+    (row 0 is the biggest hub, i.e. a cut row) go to the carry buffer raw; SBLAS_SPMV_VSELL=0 keeps SPLIT."""
+    import torch
+    K, S = sblas.kernels, sblas.synth
+    td = torch.float64 if dtype == np.float64 else torch.float32
+    rows, cols, drp, dci, dv = S.rmat(17, 16, td, dev)
+    rp, ci, v = drp.cpu().numpy(), dci.cpu().numpy(), dv.cpu().numpy()
+    nnz = len(ci)
+    assert nnz >= (1 << 20)
+    rng = np.random.default_rng(3)
+    x, y0 = rng.random(cols).astype(dtype), rng.random(rows).astype(dtype)
+    dx = _t(dev, x)
+    monkeypatch.setenv("SBLAS_SPMV_VSELL", "0")
+    p0 = K.Plan(drp, nnz).prepare(dci, cols, v.itemsize)
+    assert p0.build_colpanels(dci, dv, cols) == (0, 0)
+    monkeypatch.setenv("SBLAS_SPMV_VSELL", "1")
+    plan = K.Plan(drp, nnz).prepare(dci, cols, v.itemsize)
+    assert plan.stats()["max_row_nnz"] > 1024
+    n, W = plan.build_colpanels(dci, dv, cols)
+    is_sell, stored = plan.colpanel_format()
+    assert n == 1 and is_sell and nnz <= stored <= 1.05 * nnz + rows, (n, is_sell, stored, nnz)
+    alpha, beta = dtype(1.25), dtype(-0.75)
+    ref = oracle.spmv(rp, ci, v, x, y0.copy(), alpha, beta)
+    raw = oracle.spmv(rp, ci, v, x, np.zeros(rows, dtype), dtype(1), dtype(0))
+    bound = _row_bound(oracle, rp, ci, v, x, alpha, beta, y0)
+    dy, rep = _t(dev, y0), _t(dev, np.full(rows, -3.0, dtype))
+    K.spmv(drp, dci, dv, dx, dy, alpha, beta, plan=plan, opts=sblas.make_opts(replicas=[rep.data_ptr()]))
+    torch.cuda.synchronize()
+    got = dy.cpu().numpy()
+    _check(got, ref, bound, dtype)
+    assert np.array_equal(rep.cpu().numpy(), got)
+    short = (rp[1:] - rp[:-1]) <= 128          # uncut rows: one lane, storage order -> bit-identical
+    assert np.array_equal(got[short], ref[short])
+    # a second call on the same plan (the piece buffer is reused), with partial first / last rows
+    dy2 = _t(dev, y0)
+    carry = torch.full((8,), -1.0, dtype=td, device=dev)
+    K.spmv(drp, dci, dv, dx, dy2, alpha, beta, plan=plan,
+           opts=sblas.make_opts(flags=sblas.FLAG_HEAD_PARTIAL | sblas.FLAG_TAIL_PARTIAL, carry=carry.data_ptr()))
+    torch.cuda.synchronize()
+    y2, c = dy2.cpu().numpy(), carry.cpu().numpy()
+    assert np.array_equal(y2[1:-1], got[1:-1]) and y2[0] == y0[0] and y2[-1] == y0[-1]
+    rb = _row_bound(oracle, rp, ci, v, x, dtype(1), dtype(0), np.zeros(rows, dtype))
+    assert abs(c[0] - raw[0]) <= TOL[np.dtype(dtype)] * rb[0] and abs(c[4] - raw[-1]) <= TOL[np.dtype(dtype)] * rb[-1]
+
+
+@pytest.mark.gpu
 def test_spmv_column_panels_partials(sblas, dev, oracle):
     """HEAD / TAIL partial rows of a multi-GPU segment go to the carry buffer from the LAST panel pass (raw sums)."""
     import torch
