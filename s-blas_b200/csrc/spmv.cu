@@ -639,20 +639,34 @@ spmv_sell_kernel(int32_t n_slices, const int32_t* __restrict__ sptr, const int32
   }
 }
 
-// virtual-row form: adds the pieces of every cut row (one warp per row; lane-strided partial sums, shuffle tree:
-// a fixed order) and finishes the row through the fused epilogue
+// virtual-row form: adds the pieces of every cut row in a fixed order and finishes the row through the fused
+// epilogue.  One THREAD per cut row while it has at most 32 pieces (most cut rows have 2-3: a warp per row spent its
+// time in shuffle trees, 32 us on config 4); the few hub rows left are then taken one after the other by the whole
+// warp (lane-strided partial sums + shuffle tree).
 template <typename T>
 __global__ void __launch_bounds__(256)
 spmv_vsell_fixup_kernel(const int32_t* __restrict__ split, int32_t n_split, const T* __restrict__ piece, RowSink<T> sink) {
   const int lane = threadIdx.x & 31;
-  const int64_t w = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
-  if (w >= n_split) return;
-  const int32_t row = split[3 * w], p0 = split[3 * w + 1], n = split[3 * w + 2];
-  T s = 0;
-  for (int32_t i = lane; i < n; i += 32) s += piece[p0 + i];
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  const bool valid = i < n_split;
+  int32_t row = 0, p0 = 0, n = 0;
+  if (valid) { row = split[3 * i]; p0 = split[3 * i + 1]; n = split[3 * i + 2]; }
+  if (valid && n <= 32) {
+    T s = 0;
+    for (int32_t k = 0; k < n; ++k) s += piece[p0 + k];
+    sink.put(row, s);
+  }
+  unsigned m = __ballot_sync(0xffffffffu, valid && n > 32);
+  while (m) {
+    const int src = __ffs(m) - 1;
+    m &= m - 1;
+    const int32_t r2 = __shfl_sync(0xffffffffu, row, src), pp = __shfl_sync(0xffffffffu, p0, src), nn = __shfl_sync(0xffffffffu, n, src);
+    T s = 0;
+    for (int32_t k = lane; k < nn; k += 32) s += piece[pp + k];
 #pragma unroll
-  for (int m = 16; m > 0; m >>= 1) s += __shfl_xor_sync(0xffffffffu, s, m);
-  if (lane == 0) sink.put(row, s);
+    for (int w = 16; w > 0; w >>= 1) s += __shfl_xor_sync(0xffffffffu, s, w);
+    if (lane == 0) sink.put(r2, s);
+  }
 }
 
 // ---- VECTOR: G lanes per row, straight from global memory ----------------------------------
@@ -1245,7 +1259,7 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
         cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) { set_error("spmv sell launch: %s", cudaGetErrorString(e)); rc = 3; }
         if (rc == 0 && sl.n_split > 0) {
-          spmv_vsell_fixup_kernel<T><<<(int)ceil_div((int64_t)sl.n_split * 32, 256), 256, 0, st>>>(sl.d_split, sl.n_split, (const T*)sl.d_piece, ps);
+          spmv_vsell_fixup_kernel<T><<<(int)ceil_div((int64_t)sl.n_split, 256), 256, 0, st>>>(sl.d_split, sl.n_split, (const T*)sl.d_piece, ps);
           ++g_launches;
           e = cudaGetLastError();
           if (e != cudaSuccess) { set_error("spmv vsell fixup launch: %s", cudaGetErrorString(e)); rc = 3; }
