@@ -907,6 +907,8 @@ def run_ours(args):
                            "achieved_gbs": r["roofline"]["achieved"], "traffic": r["roofline"]["traffic"],
                            "kernel_ms_per_step": r["roofline"]["kernel_ms_per_step"],
                            "stitch": r["config_extra"].get("stitch"),
+                           "colpanels(n, cols)": r["config_extra"].get("colpanels(n, cols)"),
+                           "rowblocks(R, blocks, fill)": r["config_extra"].get("rowblocks(R, blocks, fill)"),
                            "parity": r.get("parity")})
     ok = main.get("parity", {}).get("ok", True) and all((o.get("parity") or {}).get("ok", True) for o in others)
     if env.rank == 0:

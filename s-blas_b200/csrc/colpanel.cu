@@ -234,10 +234,9 @@ struct DevBuf {  // frees a temporary on every exit path
 
 // returns 0 and fills *sl (caller frees on failure too); *kept = false when the form pads too much
 template <typename T>
-static int build_vsell(cudaStream_t st, const sblasPlan_st* plan, const int32_t* ci, const T* val, ColPanels::Sell* sl, bool* kept) {
+static int build_vsell(cudaStream_t st, int32_t rows, const int32_t* rp, int64_t nnz, const int32_t* ci, const T* val,
+                       ColPanels::Sell* sl, bool* kept) {
   *kept = false;
-  const int32_t rows = plan->rows;
-  const int32_t* rp = plan->d_rowptr;
   DevBuf nch1, npc, tmp, vstart, vkey, vkey2, vinfo, order_in, order, cnt;
   if (nch1.alloc(sizeof(int32_t) * ((size_t)rows + 1)) || npc.alloc(sizeof(int32_t) * ((size_t)rows + 1)) || cnt.alloc(16)) {
     set_error("plan_build_colpanels: out of device memory"); cudaGetLastError(); return 1;
@@ -296,7 +295,7 @@ static int build_vsell(cudaStream_t st, const sblasPlan_st* plan, const int32_t*
   sl->padded = total;
   sl->n_split = n_split;
   sl->n_piece = n_piece;
-  if ((int64_t)total * 4 > plan->nnz * 5 + (int64_t)rows) return 0;   // pads >= 25 %: not kept
+  if ((int64_t)total * 4 > nnz * 5 + (int64_t)rows) return 0;   // pads >= 25 %: not kept
   SBLAS_CUDA(cudaMalloc(&sl->d_col, sizeof(int32_t) * (size_t)std::max(total, 4)));
   SBLAS_CUDA(cudaMalloc(&sl->d_val, sizeof(T) * (size_t)std::max(total, 4)));
   vs_fill_kernel<T><<<(int)ceil_div(n_pos, 256), 256, 0, st>>>(ci, val, (const uint32_t*)vkey2.p, (const int32_t*)order.p,
@@ -379,7 +378,7 @@ static int build_colpanels(cudaStream_t st, sblasPlan_st* plan, const int32_t* c
   if ((int64_t)rows + plan->nnz / kVsellPiece + 1 >= (1ll << 31) - kVsellWindow) return 0;
   ColPanels::Sell sl;
   bool kept = false;
-  if (build_vsell<T>(st, plan, ci, val, &sl, &kept) != 0 || !kept) {
+  if (build_vsell<T>(st, rows, plan->d_rowptr, plan->nnz, ci, val, &sl, &kept) != 0 || !kept) {
     ColPanels::free_sell(sl);
     cudaGetLastError();
     return 0;
@@ -476,6 +475,16 @@ static int build_colpanels_n(cudaStream_t st, sblasPlan_st* plan, const int32_t*
     for (int p = 0; p < P && ok; ++p) {
       const int64_t off = cp.nnz_off[(size_t)p];
       if ((int64_t)tot[(size_t)p] * 5 / 4 + (int64_t)kSellC * rows / 8 >= (1ll << 31)) { ok = false; break; }
+      // rows sorted by length in windows of 65 536 by the virtual-row builder (padding < 1 %; rows above 128 nnz cut):
+      // against the 256-row block sort below c3v 2.835 -> 2.699 ms, c2 69.8 -> 68.6 us, b32 level
+      // (profiles/r02_exp_sell_window_sort.log).  SBLAS_COLPANEL_SORT=0 keeps the 256-row windows.
+      const char* esrt = getenv("SBLAS_COLPANEL_SORT");
+      if (!(esrt && atoi(esrt) == 0)) {
+        bool kept = false;
+        if (build_vsell<T>(st, rows, cp.d_rowptr + (size_t)p * ((size_t)rows + 1), tot[(size_t)p], cp.d_colidx + off,
+                           (const T*)cp.d_val + off, &cp.sell[(size_t)p], &kept)) return fail(4);
+        if (!kept) { ok = false; break; }
+      } else
       if (build_sell<T>(st, rows, cp.d_rowptr + (size_t)p * ((size_t)rows + 1), cp.d_colidx + off, (const T*)cp.d_val + off,
                         &cp.sell[(size_t)p])) return fail(4);
       padded += cp.sell[(size_t)p].padded;

@@ -651,10 +651,15 @@ spmv_vsell_fixup_kernel(const int32_t* __restrict__ split, int32_t n_split, cons
   const bool valid = i < n_split;
   int32_t row = 0, p0 = 0, n = 0;
   if (valid) { row = split[3 * i]; p0 = split[3 * i + 1]; n = split[3 * i + 2]; }
+  // phase 0: the fused epilogue; column-panel passes (phases 1-3): the pieces continue the sum carried in part[]
+  auto emit = [&](int32_t r, T s) {
+    if (sink.phase == 0) sink.put(r, s);
+    else sink.put_y(r, sink.phase >= 2 ? add_rn(sink.part[r], s) : s, T(0));
+  };
   if (valid && n <= 32) {
     T s = 0;
     for (int32_t k = 0; k < n; ++k) s += piece[p0 + k];
-    sink.put(row, s);
+    emit(row, s);
   }
   unsigned m = __ballot_sync(0xffffffffu, valid && n > 32);
   while (m) {
@@ -665,7 +670,26 @@ spmv_vsell_fixup_kernel(const int32_t* __restrict__ split, int32_t n_split, cons
     for (int32_t k = lane; k < nn; k += 32) s += piece[pp + k];
 #pragma unroll
     for (int w = 16; w > 0; w >>= 1) s += __shfl_xor_sync(0xffffffffu, s, w);
-    if (lane == 0) sink.put(r2, s);
+    if (lane == 0) emit(r2, s);
+  }
+}
+
+// G lanes per cut row (lane-strided partial sums, shuffle tree: a fixed order).  Measured on config 4 (same box, ms per
+// step): 8 lanes per row 0.543, one warp per row 0.560, one thread per row 0.568 (profiles/r02_exp_c4_fixup.log)
+template <typename T, int G>
+__global__ void __launch_bounds__(256)
+spmv_vsell_fixup_group_kernel(const int32_t* __restrict__ split, int32_t n_split, const T* __restrict__ piece, RowSink<T> sink) {
+  const int lane = threadIdx.x & (G - 1);
+  const int64_t w = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) / G;
+  const bool valid = w < n_split;
+  const int32_t row = valid ? split[3 * w] : 0, p0 = valid ? split[3 * w + 1] : 0, n = valid ? split[3 * w + 2] : 0;
+  T s = 0;
+  for (int32_t i = lane; i < n; i += G) s += piece[p0 + i];
+#pragma unroll
+  for (int m = G / 2; m > 0; m >>= 1) s += __shfl_xor_sync(0xffffffffu, s, m);
+  if (lane == 0 && valid) {
+    if (sink.phase == 0) sink.put(row, s);
+    else sink.put_y(row, sink.phase >= 2 ? add_rn(sink.part[row], s) : s, T(0));
   }
 }
 
@@ -1259,7 +1283,14 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
         cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) { set_error("spmv sell launch: %s", cudaGetErrorString(e)); rc = 3; }
         if (rc == 0 && sl.n_split > 0) {
-          spmv_vsell_fixup_kernel<T><<<(int)ceil_div((int64_t)sl.n_split, 256), 256, 0, st>>>(sl.d_split, sl.n_split, (const T*)sl.d_piece, ps);
+          // lanes per cut row: SBLAS_VSELL_FIXUP = 8 (default) / 32 / 1 (a thread per row, the warp for hub rows)
+          static const int fix_g = [] { const char* e = getenv("SBLAS_VSELL_FIXUP"); return e ? atoi(e) : 8; }();
+          if (fix_g == 1)
+            spmv_vsell_fixup_kernel<T><<<(int)ceil_div((int64_t)sl.n_split, 256), 256, 0, st>>>(sl.d_split, sl.n_split, (const T*)sl.d_piece, ps);
+          else if (fix_g == 32)
+            spmv_vsell_fixup_group_kernel<T, 32><<<(int)ceil_div((int64_t)sl.n_split * 32, 256), 256, 0, st>>>(sl.d_split, sl.n_split, (const T*)sl.d_piece, ps);
+          else
+            spmv_vsell_fixup_group_kernel<T, 8><<<(int)ceil_div((int64_t)sl.n_split * 8, 256), 256, 0, st>>>(sl.d_split, sl.n_split, (const T*)sl.d_piece, ps);
           ++g_launches;
           e = cudaGetLastError();
           if (e != cudaSuccess) { set_error("spmv vsell fixup launch: %s", cudaGetErrorString(e)); rc = 3; }

@@ -681,7 +681,9 @@ def test_spmv_column_panels(sblas, dev, oracle, dtype, mat, panels, fmt, monkeyp
                opts=sblas.make_opts(lanes=lanes, replicas=[rep.data_ptr()]))
         torch.cuda.synchronize()
         got = dy.cpu().numpy()
-        _check(got, ref, bound, dtype, exact=(lanes == 1 or is_sell))   # one lane per row walks it in CSR order
+        # one lane per row walks it in CSR order: bit-identical (sliced-ELL: for rows of <= 128 nnz per panel, longer ones are cut)
+        longest = int((rp[1:] - rp[:-1]).max()) if h else 0
+        _check(got, ref, bound, dtype, exact=(longest <= 128 if is_sell else lanes == 1))
         assert np.array_equal(rep.cpu().numpy(), got)
     # the plain kernel is still there on request, and agrees
     dy = _t(dev, y0)
