@@ -388,6 +388,7 @@ static int build_colpanels(cudaStream_t st, sblasPlan_st* plan, const int32_t* c
   cp.panel_cols = (int32_t)(((int64_t)cols + 31) & ~(int64_t)31);
   cp.is_f64 = sizeof(T) == 8;
   cp.sell.assign(1, sl);
+  cp.skewed = true;
   return 0;
 }
 

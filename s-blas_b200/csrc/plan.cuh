@@ -93,6 +93,7 @@ struct ColPanels {
     sl = Sell();
   }
   std::vector<Sell> sell;
+  bool skewed = false;   // the single virtual-row panel of a skewed input (AUTO keeps SPLIT for it when replicas are written)
 };
 
 }  // namespace sblas

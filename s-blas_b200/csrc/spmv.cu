@@ -693,6 +693,17 @@ spmv_vsell_fixup_group_kernel(const int32_t* __restrict__ split, int32_t n_split
   }
 }
 
+// rows [a, b) of the finished local y -> the same rows of every replica (peer mappings or one multicast address):
+// consecutive lanes, consecutive elements — 128 / 256 contiguous bytes per warp store
+template <typename T>
+__global__ void __launch_bounds__(256)
+spmv_replicate_kernel(const T* __restrict__ y, int32_t a, int32_t b, OutSpec<T> out) {
+  for (int64_t i = a + blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < b; i += (int64_t)gridDim.x * blockDim.x) {
+    const T v = y[i];
+    for (int d = 0; d < out.n; ++d) out.ptr[d][i] = v;
+  }
+}
+
 // ---- VECTOR: G lanes per row, straight from global memory ----------------------------------
 template <typename T, int G, int BLOCK, bool FMA>
 __global__ void __launch_bounds__(BLOCK)
@@ -1234,7 +1245,12 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
   if (variant == SBLAS_SPMV_COLPANEL)
     SBLAS_CHECK(have_panels, "spmv: SBLAS_SPMV_COLPANEL needs a plan with column panels of this value type (sblas_plan_build_colpanels_*)");
   bool auto_gather = false;
-  if (!user_variant && have_panels) {
+  // a skewed input's virtual-row panel finishes rows in sorted order: as REMOTE stores (replicas) every 4-byte
+  // element would be an NVLink transaction of its own, and a separate coalesced copy afterwards does not overlap
+  // with the compute (config 4, 2 / 4 GPUs: SPLIT with in-kernel peer stores 0.364 / 0.203 ms, the mirror with
+  // scattered stores 0.356 / 0.406 ms, with a copy kernel afterwards 0.406 / 0.272 ms): with replicas AUTO keeps SPLIT
+  const bool skip_mirror = have_panels && plan->cp.skewed && sink.out.n > 0;
+  if (!user_variant && have_panels && !skip_mirror) {
     variant = SBLAS_SPMV_COLPANEL;
   } else if (plan && variant == SBLAS_SPMV_PIPE && !user_variant &&
              measure_gather_heavy(st, plan, rp, ci, rows, cols, sizeof(T))) {
@@ -1257,8 +1273,15 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
     const ColPanels& cp = plan->cp;
     sblasOpts po;
     if (o) { po = *o; po.tile = 0; }   // the panels' tile tables were sized at build time
+    // sliced-ELL passes finish rows in sorted order (windows of up to 65 536 rows) and store them to the replicas from
+    // the kernel, overlapped with the compute.  SBLAS_SELL_REPLICATE_AFTER=1: the passes write the local y only and one
+    // coalesced copy kernel pushes the finished rows to every replica afterwards (measured slower on config 4: the
+    // copy does not overlap).
+    static const int env_rep_after = [] { const char* e = getenv("SBLAS_SELL_REPLICATE_AFTER"); return e ? atoi(e) : 0; }();
+    const bool replicate_after = env_rep_after != 0 && sink.out.n > 0 && !cp.sell.empty();   // opt-in (experiments)
     for (int p = 0; p < cp.n && rc == 0; ++p) {
       RowSink<T> ps = sink;
+      if (replicate_after) ps.out.n = 0;
       ps.part = (T*)cp.d_part;
       ps.phase = cp.n == 1 ? 0 : p == 0 ? 1 : p == cp.n - 1 ? 3 : 2;
       ps.stage_src = ps.phase == 0 ? y : ps.phase == 1 ? nullptr : (const T*)cp.d_part;
@@ -1303,6 +1326,17 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
       rc = launch_pipe<T>(st, sub, rows, sub->nnz, sub->d_rowptr, cp.d_colidx + off, (const T*)cp.d_val + off, x, ps,
                           o ? &po : nullptr, false, &fb, true);
       if (rc == 0 && fb != 0) { set_error("spmv: column panel %d cannot be staged by the PIPE kernel", p); rc = 5; }
+    }
+    if (rc == 0 && replicate_after) {
+      // rows that went to the carry buffer (partial first / last row of a segment) are not the replicas' business
+      const int32_t a = (flags & SBLAS_FLAG_HEAD_PARTIAL) ? 1 : 0, b = rows - ((flags & SBLAS_FLAG_TAIL_PARTIAL) ? 1 : 0);
+      if (b > a) {
+        const int grid = (int)std::min<int64_t>(ceil_div((int64_t)(b - a), 256), (int64_t)kNumSM * 16);
+        spmv_replicate_kernel<T><<<grid, 256, 0, st>>>(y, a, b, sink.out);
+        ++g_launches;
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) { set_error("spmv replicate launch: %s", cudaGetErrorString(e)); rc = 3; }
+      }
     }
     return rc;
   }

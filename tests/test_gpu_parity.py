@@ -747,13 +747,24 @@ def test_spmv_virtual_row_sell_on_skewed_rows(sblas, dev, oracle, dtype, monkeyp
     raw = oracle.spmv(rp, ci, v, x, np.zeros(rows, dtype), dtype(1), dtype(0))
     bound = _row_bound(oracle, rp, ci, v, x, alpha, beta, y0)
     dy, rep = _t(dev, y0), _t(dev, np.full(rows, -3.0, dtype))
-    K.spmv(drp, dci, dv, dx, dy, alpha, beta, plan=plan, opts=sblas.make_opts(replicas=[rep.data_ptr()]))
+    # with a replica to write AUTO keeps SPLIT for a skewed input (sorted-order remote stores do not pay); the mirror
+    # is still taken on request, and by AUTO when there is no replica
+    K.spmv(drp, dci, dv, dx, dy, alpha, beta, plan=plan,
+           opts=sblas.make_opts(variant=sblas.SPMV_COLPANEL, replicas=[rep.data_ptr()]))
     torch.cuda.synchronize()
     got = dy.cpu().numpy()
     _check(got, ref, bound, dtype)
     assert np.array_equal(rep.cpu().numpy(), got)
     short = (rp[1:] - rp[:-1]) <= 128          # uncut rows: one lane, storage order -> bit-identical
     assert np.array_equal(got[short], ref[short])
+    dya = _t(dev, y0)
+    K.spmv(drp, dci, dv, dx, dya, alpha, beta, plan=plan)                     # AUTO, no replica: the mirror
+    assert np.array_equal(dya.cpu().numpy(), got)
+    dyb, repb = _t(dev, y0), _t(dev, np.full(rows, -3.0, dtype))
+    K.spmv(drp, dci, dv, dx, dyb, alpha, beta, plan=plan, opts=sblas.make_opts(replicas=[repb.data_ptr()]))   # AUTO + replica: SPLIT
+    torch.cuda.synchronize()
+    _check(dyb.cpu().numpy(), ref, bound, dtype)
+    assert np.array_equal(repb.cpu().numpy(), dyb.cpu().numpy())
     # a second call on the same plan (the piece buffer is reused), with partial first / last rows
     dy2 = _t(dev, y0)
     carry = torch.full((8,), -1.0, dtype=td, device=dev)
