@@ -1,26 +1,27 @@
-// colpanel.cu — column-panel device mirror of A for gather-heavy SpMV (x larger than L2).
+// colpanel.cu — the sliced-ELL device mirror of A that CsrSparseMatrix::sync2gpu builds for SpMV
+// ("matrix.h: device CSR layout and padding" is one of the subsystems the north star lets change).
 //
-// Why: the north star's SpMV shape (16M rows x 32 nnz/row, uniform-random columns, fp64) has an x of
-// 134 MB against a 126 MB L2, and consecutive rows look at unrelated parts of it: every x gather is a
-// 32-byte DRAM sector of its own (536.9 M x 32 B = 17 GB of sector traffic beside 6.9 GB of compulsory
-// bytes), the kernel is bound by DRAM gathers in flight and sits at 19 % of the HBM roofline.  The lever
-// is the cache, and it is a data-layout question ("matrix.h: device CSR layout and padding" is one of
-// the subsystems the north star lets change): next to the CSR arrays the reference's API exposes,
-// sync2gpu builds a mirror of A split into P COLUMN PANELS, panel p = the nonzeros whose column lies in
-// [p*W, (p+1)*W), each panel a CSR of its own (row pointers [rows+1], col_idx / val in the original
-// order within a row).  y = beta*y + alpha*A*x then runs as P back-to-back passes of the PIPE kernel, pass p
-// touching only x[p*W, (p+1)*W) — a slice sized to stay L2-resident (default <= 48 MB of the 126 MB L2)
-// while its panel of A streams by — and carrying the RAW running row sums in a scratch
-// vector: pass 0 writes sum_0, pass p continues the accumulation FROM the carried value (so a row
-// summed by one lane still adds its products in CSR storage order, one rounded multiply and one
-// rounded add each: bit-identical to spmv.h:24-30 when the row's columns ascend), the last pass
-// applies alpha and beta.  Extra traffic: P x (row pointers + carried sums read and written) =
-// P x 20 B per row, i.e. +19 % on the compulsory bytes at P = 4.
+// The mirror is a list of P column panels; panel p holds the nonzeros whose column lies in [p*W, (p+1)*W), every row's
+// entries in their original order.  Each panel is stored in sliced-ELL form (SELL-32, rows sorted by length inside
+// windows of 65 536): 32-row slices stored column-major, so a lane that walks ITS row front to back reads coalesced
+// lines with its 31 neighbours, rows above 128 nnz cut into pieces whose raw sums a fix-up kernel adds.  spmv.cu's
+// spmv_sell_kernel runs one pass per panel.  Three set-ups, chosen by sblas_plan_build_colpanels_*(n_panels = 0):
 //
-// Built automatically (sblas_plan_build_colpanels_*, n_panels = 0) in two cases: gather-heavy inputs (x larger than
-// 96 MB and the plan's column-locality statistic says consecutive rows are far apart, col_jump > cols / 256) get
-// P >= 2 panels; every other input of >= 1M nnz whose rows fit the sliced-ELL form gets ONE panel, because the
-// barrier-free per-lane kernel over coalesced slices also beats the staged kernel on regular rows (see below).
+//   gather-heavy inputs (x larger than 96 MB and consecutive rows far apart, col_jump > cols / 256; the north star's
+//     16M x 32 uniform-random shape: x = 134 MB against a 126 MB L2, every gather its own 32-byte DRAM sector, 19 % of
+//     the HBM roofline): P >= 2 panels, x slices of <= 48 MB that stay L2-RESIDENT while their panel streams by.
+//     y = beta*y + alpha*A*x runs as P back-to-back passes that carry the RAW running row sums in part[]: pass 0
+//     writes sum_0, pass p continues the accumulation FROM the carried value (a row is still summed in CSR storage
+//     order, one rounded multiply and one rounded add per term: bit-identical to spmv.h:24-30 when the row's columns
+//     ascend), the last pass applies alpha and beta.  5.63 -> 2.67 ms.
+//   regular inputs of >= 2^20 nnz (padding < 25 %, no row above 4096 nnz): ONE panel — the per-lane kernel over
+//     coalesced slices needs no staging, barrier or shared memory and beats the TMA-staged PIPE kernel: banded
+//     16M x 32 1.33-1.46 -> 1.08 ms (97 % of the measured HBM copy rate), 2-D Laplacian 76 -> 69-73 us.
+//   skewed inputs (R-MAT): one panel in the VIRTUAL-ROW form (build_vsell below): 0.598 -> 0.543 ms.
+//
+// CSR panels run by the staged PIPE kernel remain as the fallback when the sliced-ELL form pads >= 25 %
+// (SBLAS_COLPANEL_SELL=0 forces them).  A mirror is an optimisation: in automatic mode no failure to build one (memory,
+// limits) is an error, the plain kernels then take the input.
 #include <cub/cub.cuh>
 
 #include "plan.cuh"

@@ -4,7 +4,10 @@
 // kernel.h:28-37) of the reference; the CPU statement of the same arithmetic is
 // sblas_spmv_csr_cpu (spmv.h:16-32).
 //
-// Three variants (sblasOpts.variant, AUTO picks from the plan's row statistics):
+// Variants (sblasOpts.variant; AUTO picks from the plan's row statistics and mirrors).  Since round 2 the first
+// choice is SELL / COLPANEL (spmv_sell_kernel below + colpanel.cu): a lane per row over the sliced-ELL mirror that
+// sync2gpu builds — one panel for regular inputs, column panels with L2-resident x slices for gather-heavy ones, the
+// virtual-row form for skewed ones.  Without a mirror:
 //
 //  TILE   nnz-balanced, row-aligned merge-path tiles (plan.cuh).  A CTA streams its tile's
 //         col_idx / val with 128-bit L1-bypassing loads (fully coalesced whatever the row
