@@ -277,6 +277,22 @@ def test_compute_fails_loudly_without_gpu(sblas):
     assert rc != 0 and L.lib().sblas_last_error()          # error, not a silent CPU path
     with pytest.raises(L.SblasError):
         L.check(rc, "plan_create")
+    # the entry points added in round 2 fail the same way (no silent host path): the allocation-free SpMV, the
+    # streamed dense transfers, the managed allocator
+    x = np.zeros(8)
+    vp = lambda a: a.ctypes.data_as(C.c_void_p)
+    rc = L.lib().sblas_spmv_csr_noalloc_f64(None, C.c_int32(2), C.c_int32(2), C.c_int64(0), vp(rp), vp(rp), vp(x), vp(x), vp(x),
+                                            C.c_double(1.0), C.c_double(0.0))
+    assert rc != 0 and L.lib().sblas_last_error()
+    rc = L.lib().sblas_dense_upload_rows_f64(None, vp(x), C.c_int64(4), C.c_int64(0), C.c_int64(4), C.c_int32(2), vp(x), C.c_int64(2))
+    assert rc != 0
+    p = C.c_void_p()
+    assert L.lib().sblas_managed_alloc(C.c_size_t(64), C.byref(p)) != 0
+    # ... while the process-wide switches and the NVTX ranges are host-only and harmless without a device
+    prev = L.lib().sblas_set_spmm_exact(C.c_int(1))
+    assert L.lib().sblas_set_spmm_exact(C.c_int(prev)) == 1
+    L.lib().sblas_range_push(b"test")
+    L.lib().sblas_range_pop()
 
 
 def test_python_mirror_api_surface(sblas):
