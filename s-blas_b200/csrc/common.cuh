@@ -125,6 +125,44 @@ __device__ __forceinline__ float ldg_stream(const float* p) {
   return r;
 }
 
+// L2 eviction policies (createpolicy) and loads that carry one: streamed operands are marked evict_first, gathered
+// ones evict_last, so a slice of x that is meant to stay L2-resident is not pushed out by the matrix streaming by
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_last() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ int ldg_stream_hint(const int* p, uint64_t pol) {
+  int r;
+  asm("ld.global.nc.L1::no_allocate.L2::cache_hint.s32 %0, [%1], %2;" : "=r"(r) : "l"(p), "l"(pol));
+  return r;
+}
+__device__ __forceinline__ double ldg_stream_hint(const double* p, uint64_t pol) {
+  double r;
+  asm("ld.global.nc.L1::no_allocate.L2::cache_hint.f64 %0, [%1], %2;" : "=d"(r) : "l"(p), "l"(pol));
+  return r;
+}
+__device__ __forceinline__ float ldg_stream_hint(const float* p, uint64_t pol) {
+  float r;
+  asm("ld.global.nc.L1::no_allocate.L2::cache_hint.f32 %0, [%1], %2;" : "=f"(r) : "l"(p), "l"(pol));
+  return r;
+}
+__device__ __forceinline__ double ldg_hint(const double* p, uint64_t pol) {
+  double r;
+  asm("ld.global.nc.L2::cache_hint.f64 %0, [%1], %2;" : "=d"(r) : "l"(p), "l"(pol));
+  return r;
+}
+__device__ __forceinline__ float ldg_hint(const float* p, uint64_t pol) {
+  float r;
+  asm("ld.global.nc.L2::cache_hint.f32 %0, [%1], %2;" : "=f"(r) : "l"(p), "l"(pol));
+  return r;
+}
+
 // 16-byte vector type of T
 template <typename T> struct Vec16;
 template <> struct Vec16<double> { using type = double2; static constexpr int N = 2; };

@@ -604,12 +604,15 @@ spmv_pipe_kernel(const int32_t* __restrict__ tile_row, const int32_t* __restrict
 // storage order with separately rounded multiply and add, continuing from the sum carried over from the
 // previous panels: bit-identical to spmv.h:24-30 when the row's columns ascend.  No shared memory, no
 // barrier; the 256 KB of the SM stay L1 for the gathers in flight.  Padding entries carry col = -1.
-template <typename T, int U>
+// HINT: L2 eviction policies on the loads — the panel's col / val evict_first, the x gathers evict_last
+template <typename T, int U, bool HINT = false>
 __global__ void __launch_bounds__(kSellSigma)
 spmv_sell_kernel(int32_t n_slices, const int32_t* __restrict__ sptr, const int32_t* __restrict__ perm,
                  const int32_t* __restrict__ col, const T* __restrict__ val, const T* __restrict__ x,
                  RowSink<T> sink, T* __restrict__ piece) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint64_t pol_a = 0, pol_x = 0;
+  if (HINT) { pol_a = l2_policy_evict_first(); pol_x = l2_policy_evict_last(); }
   constexpr int SPW = kSellSigma / kSellC;  // slices per window
   for (int64_t sl = (int64_t)blockIdx.x * SPW + warp; sl < n_slices; sl += (int64_t)gridDim.x * SPW) {
     const int32_t p0 = __ldg(sptr + sl), p1 = __ldg(sptr + sl + 1);
@@ -622,13 +625,13 @@ spmv_sell_kernel(int32_t n_slices, const int32_t* __restrict__ sptr, const int32
       for (int u = 0; u < U; ++u) {
         c[u] = -1;
         if (p + u * kSellC < p1) {
-          c[u] = ldg_stream(col + p + u * kSellC);
-          v[u] = ldg_stream(val + p + u * kSellC);
+          c[u] = HINT ? ldg_stream_hint(col + p + u * kSellC, pol_a) : ldg_stream(col + p + u * kSellC);
+          v[u] = HINT ? ldg_stream_hint(val + p + u * kSellC, pol_a) : ldg_stream(val + p + u * kSellC);
         }
       }
 #pragma unroll
       for (int u = 0; u < U; ++u)
-        if (c[u] >= 0) xv[u] = __ldg(x + c[u]);
+        if (c[u] >= 0) xv[u] = HINT ? ldg_hint(x + c[u], pol_x) : __ldg(x + c[u]);
 #pragma unroll
       for (int u = 0; u < U; ++u)
         if (c[u] >= 0) sum = add_rn(sum, mul_rn(v[u], xv[u]));
@@ -1301,6 +1304,13 @@ static int spmv_impl(cudaStream_t st, int32_t rows, int32_t cols, int64_t nnz, c
         static const int env_g = [] { const char* e = getenv("SBLAS_SELL_GRID"); return e ? atoi(e) : 0; }();   // CTAs per SM (experiments)
         const int grid = std::max(1, std::min(n_win, n_sm * (env_g > 0 ? std::min(env_g, per_sm) : per_sm)));
         // (forcing 5 / 6 resident CTAs with __launch_bounds__ spills at 48 / 40 registers: 2.97 -> 3.73 / 4.07 ms, dropped)
+        // multi-panel passes: L2 eviction policies on the loads (panel stream evict_first, x gathers evict_last) keep
+        // the x slice resident while the panel streams by: c3v 2.69 -> 2.65 ms at 3 panels, 3.10 -> 3.00 at 2
+        // (profiles/r02_exp_c3v_l2hint.log).  SBLAS_SELL_L2HINT=0 turns them off.
+        static const int env_hint = [] { const char* e = getenv("SBLAS_SELL_L2HINT"); return e ? atoi(e) : 1; }();
+        if (env_hint && cp.n > 1 && env_u == 8)
+          spmv_sell_kernel<T, 8, true><<<grid, kSellSigma, 0, st>>>(sl.n_slices, sl.d_sptr, sl.d_perm, sl.d_col, (const T*)sl.d_val, x, ps, (T*)sl.d_piece);
+        else
         if (env_u == 8) spmv_sell_kernel<T, 8><<<grid, kSellSigma, 0, st>>>(sl.n_slices, sl.d_sptr, sl.d_perm, sl.d_col, (const T*)sl.d_val, x, ps, (T*)sl.d_piece);
         else if (env_u == 2) spmv_sell_kernel<T, 2><<<grid, kSellSigma, 0, st>>>(sl.n_slices, sl.d_sptr, sl.d_perm, sl.d_col, (const T*)sl.d_val, x, ps, (T*)sl.d_piece);
         else
